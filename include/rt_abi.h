@@ -1,0 +1,258 @@
+/*
+ * rt_abi.h — C ABI of librt_b200.so: the sm_100a replacement for the reference's
+ * per-pixel ray-tracing compute pass (shader/raytracingCs.glsl).
+ *
+ * The reference has no FFI; its "operator surface" for this pass is the GL binding
+ * state set up at ONE call site, src/ForwardShadingPipeline.cpp:155-180:
+ *   - Object[]  SSBO binding 0      (src/SSBO.h:16-23,      stride 176 B)
+ *   - Light[]   SSBO binding 1      (src/LightSSBO.h:16-25, stride  96 B)
+ *   - 13 uniforms                   (src/ForwardShadingPipeline.cpp:156-166,
+ *                                    shader/raytracingCs.glsl:72-89)
+ *   - 3 output images               (src/ForwardShadingPipeline.cpp:57-65,115-126)
+ *   - cubemap + noise samplers      (src/ForwardShadingPipeline.cpp:39-49,167-170)
+ *   - glDispatchCompute + barrier   (src/ForwardShadingPipeline.cpp:175-180)
+ * Every entry point below names the reference interface it replaces.
+ *
+ * Conventions: plain C, no torch / CUDA types in signatures; every call returns an
+ * rt_status and never throws or exits; the library copies what it is given and never
+ * frees caller memory; a context is bound to one CUDA device and one caller thread at
+ * a time. There is NO CPU fallback: without a CUDA device rt_create fails.
+ */
+#ifndef RT_ABI_H_
+#define RT_ABI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* ------------------------------------------------------------------------- */
+/* Data contracts: byte-exact std430 layouts (== the alignas() C++ structs).   */
+/* ------------------------------------------------------------------------- */
+
+/* src/Material.h:11-23  <->  shader/raytracingCs.glsl:20-32   (80 B, align 16) */
+typedef struct rt_material {
+  int32_t type;              /*  0  never read by the shader                    */
+  int32_t _pad0[3];          /*  4                                             */
+  float   albedo[3];         /* 16                                             */
+  float   metallic;          /* 28                                             */
+  float   roughness;         /* 32                                             */
+  float   diffuseStrength;   /* 36  >0 selects the diffuse-bounce branch        */
+  float   ior;               /* 40                                             */
+  float   transparency;      /* 44                                             */
+  float   specular;          /* 48  never read by the shader                    */
+  float   subsurfaceScatter; /* 52                                             */
+  int32_t _pad1[2];          /* 56                                             */
+  float   subsurfaceColor[3];/* 64                                             */
+  float   scatterDistance;   /* 76                                             */
+} rt_material;
+
+/* src/Object.h:8-11  <->  shader/raytracingCs.glsl:8-11       (32 B, align 16) */
+typedef struct rt_aabb {
+  float   min[3]; int32_t _pad0;   /*  0 */
+  float   max[3]; int32_t _pad1;   /* 16 */
+} rt_aabb;
+
+/* src/Object.h:13-21  <->  shader/raytracingCs.glsl:34-42    (176 B, align 16) */
+typedef struct rt_object {
+  int32_t type;              /*   0  0 = sphere, 1 = plane                      */
+  int32_t _pad0[3];          /*   4                                            */
+  float   position[3];       /*  16                                            */
+  float   radius;            /*  28                                            */
+  float   normal[3];         /*  32                                            */
+  int32_t _pad1;             /*  44                                            */
+  float   size[2];           /*  48                                            */
+  int32_t _pad2[2];          /*  56                                            */
+  rt_material material;      /*  64                                            */
+  rt_aabb bounds;            /* 144                                            */
+} rt_object;
+
+/* src/Light.h:7-20  <->  shader/raytracingCs.glsl:44-58       (96 B, align 16) */
+typedef struct rt_light {
+  int32_t type;              /*  0  0 = point, 1 = directional, 2 = area        */
+  int32_t _pad0[3];          /*  4                                             */
+  float   position[3];       /* 16                                             */
+  int32_t _pad1;             /* 28                                             */
+  float   direction[3];      /* 32                                             */
+  int32_t _pad2;             /* 44                                             */
+  float   color[3];          /* 48                                             */
+  float   intensity;         /* 60                                             */
+  float   radius;            /* 64  never read by the shader                    */
+  int32_t samples;           /* 68  never read by the shader                    */
+  float   shadowSoftness;    /* 72                                             */
+  int32_t shadowType;        /* 76  0 none, 1 PCF, 2 PCSS, other -> shadow 0    */
+  int32_t pcfSamples;        /* 80                                             */
+  float   lightSize;         /* 84                                             */
+  float   angularRadius;     /* 88  dead in the shader (:352 overwritten :364)  */
+  int32_t _pad3;             /* 92                                             */
+} rt_light;
+
+#define RT_OBJECT_STRIDE   176
+#define RT_LIGHT_STRIDE     96
+#define RT_MATERIAL_STRIDE  80
+
+#if defined(__cplusplus)
+static_assert(sizeof(rt_material) == 80 && sizeof(rt_aabb) == 32, "std430 layout");
+static_assert(sizeof(rt_object) == 176 && sizeof(rt_light) == 96, "std430 layout");
+static_assert(offsetof(rt_object, material) == 64 && offsetof(rt_object, bounds) == 144, "std430 layout");
+static_assert(offsetof(rt_material, subsurfaceColor) == 64 && offsetof(rt_light, shadowSoftness) == 72, "std430 layout");
+#else
+_Static_assert(sizeof(rt_material) == 80 && sizeof(rt_aabb) == 32, "std430 layout");
+_Static_assert(sizeof(rt_object) == 176 && sizeof(rt_light) == 96, "std430 layout");
+#endif
+
+/* ------------------------------------------------------------------------- */
+/* Status codes (the reference propagates no errors: src/Shader.h:132-149)     */
+/* ------------------------------------------------------------------------- */
+typedef enum rt_status {
+  RT_OK = 0,
+  RT_ERR_INVALID_ARG = 1,
+  RT_ERR_CUDA = 2,
+  RT_ERR_NCCL = 3,
+  RT_ERR_OOM = 4,
+  RT_ERR_UNAVAILABLE = 5
+} rt_status;
+
+/* rt_frame_params.flags */
+#define RT_FLAG_NORMAL_FP32     0x01u /* normal buffer is RGBA32F instead of the reference's RGBA16F   */
+#define RT_FLAG_PARITY_MATH     0x02u /* IEEE div/sqrt everywhere, no FMA contraction (-fmad=false)    */
+#define RT_FLAG_SKYBOX_HW       0x04u /* miss path through the CUDA cubemap texture object (HW filter) */
+#define RT_FLAG_COUNTERS        0x08u /* accumulate the reference-literal op counters (rt_get_counters)*/
+#define RT_FLAG_ACCUMULATE      0x10u /* colour += instead of = (sample-range partial sums) */
+#define RT_FLAG_NO_REGROUP      0x20u /* disable warp-level ray regrouping (A/B measurement only)      */
+
+/* == the shader's uniforms (shader/raytracingCs.glsl:72-89) + the compile-time constants
+ *    promoted to run time (:4 MAX_RAY_DEPTH, image size) + the sharding window.          */
+typedef struct rt_frame_params {
+  int32_t  width, height;        /* imageSize(outputImage)                                    */
+  int32_t  row_begin, row_end;   /* rows to render; full frame = 0,height. Row 0 = gl y 0      */
+  int32_t  num_objects;          /* numObjects  (src/ForwardShadingPipeline.cpp:156)          */
+  int32_t  num_lights;           /* numLights   (:157)                                        */
+  float    camera_pos[3];        /* cameraPos   (:158)                                        */
+  float    camera_dir[3];        /* cameraDir   (:159)                                        */
+  float    camera_up[3];         /* cameraUp    (:160)                                        */
+  float    camera_right[3];      /* cameraRight (:161)                                        */
+  float    fov_deg;              /* fov         (:162)  shader default 60, Camera::FOV 45     */
+  float    focal_length;         /* focalLength — never set by the host: 1.0 (glsl:80)        */
+  float    max_ray_distance;     /* maxRayDistance — never set by the host: 114514 (glsl:85)  */
+  int32_t  use_skybox;           /* useSkybox   (:166)                                        */
+  float    noise_scale[2];       /* noiseScale  (:164)  1/1024                                */
+  int32_t  frame_count;          /* frameCount  (:163)  first sample index                    */
+  int32_t  num_samples;          /* 1 = the reference; n = mean over frame_count..+n-1        */
+  int32_t  max_ray_depth;        /* #define MAX_RAY_DEPTH 3 (glsl:4)                          */
+  uint32_t flags;                /* RT_FLAG_*                                                 */
+} rt_frame_params;
+
+/* Reference-literal operation counters (flop model v0). Index into
+ * the uint64 array returned by rt_get_counters.                                  */
+enum {
+  RT_CNT_RAYS = 0,          /* intersectObjects calls (glsl:155)                   */
+  RT_CNT_AABB,              /* intersectAABB calls    (glsl:163)                   */
+  RT_CNT_SPHERE,            /* intersectSphere calls  (glsl:171)                   */
+  RT_CNT_PLANE_EARLY,       /* intersectPlane returning before the frame (glsl:122-124) */
+  RT_CNT_PLANE_FULL,        /* intersectPlane reaching the frame build (glsl:126-150)   */
+  RT_CNT_HIT_UPDATE_SPHERE, /* closest-hit updates on spheres (glsl:178-188)       */
+  RT_CNT_HIT_UPDATE_PLANE,  /* closest-hit updates on planes  (glsl:178-190)       */
+  RT_CNT_LIGHT_POINT,       /* computeLighting iterations by light type (glsl:468-489) */
+  RT_CNT_LIGHT_DIR,
+  RT_CNT_LIGHT_AREA,
+  RT_CNT_PBR,               /* computePBR calls (glsl:499)                         */
+  RT_CNT_PCF_SETUP,         /* pcfShadow calls (glsl:342)                          */
+  RT_CNT_PCF_SAMPLE,        /* pcfShadow loop iterations (glsl:362)                */
+  RT_CNT_PCSS_PROBE,        /* pcssShadow loop iterations (glsl:406)               */
+  RT_CNT_SSS_SAMPLE,        /* computeSubsurfaceScattering iterations (glsl:318)   */
+  RT_CNT_BOUNCE_MIRROR,     /* next-ray branch taken (glsl:572-576)                */
+  RT_CNT_BOUNCE_REFRACT,    /* (glsl:568-571)                                      */
+  RT_CNT_BOUNCE_DIFFUSE,    /* (glsl:555-567)                                      */
+  RT_CNT_RR,                /* Russian-roulette evaluations (glsl:544-549)         */
+  RT_CNT_CAMERA,            /* generateCameraRay calls (glsl:198)                  */
+  RT_CNT_MISS,              /* miss path taken (glsl:530-534)                      */
+  RT_CNT_COUNT
+};
+
+typedef struct rt_context rt_context;   /* opaque; one per CUDA device; NOT thread-safe */
+
+/* Library / device info. */
+int         rt_abi_version(void);
+const char* rt_status_string(rt_status s);
+
+/* Replaces ForwardShadingPipline::Init's GL setup for this pass
+ * (src/ForwardShadingPipeline.cpp:6-20: shader compile, SSBO gen, texture gen).  */
+rt_status rt_create(rt_context** out, int cuda_device);
+void      rt_destroy(rt_context* ctx);
+const char* rt_last_error(rt_context* ctx);
+
+/* Replaces SSBO::update (src/SSBO.h:16-23) + LightSSBO::update (src/LightSSBO.h:16-25):
+ * copies n Object (176-B stride) and m Light (96-B stride) records host->device and
+ * re-stages the kernel's SoA scene. The caller keeps ownership. n, m may be 0.
+ * async != 0: the copy is enqueued on `cuda_stream` from an internal pinned staging
+ * buffer and the call returns without synchronising.                               */
+rt_status rt_upload_scene(rt_context* ctx, const void* objects, int n,
+                          const void* lights, int m, void* cuda_stream, int async);
+
+/* Replaces glBindTexture(GL_TEXTURE_CUBE_MAP, ...) (src/ForwardShadingPipeline.cpp:167-170)
+ * and the finished faces ConvertHDRToCubemap produces (src/TextureLoader.cpp:118-194).
+ * faces: 6 x face_size x face_size x channels, order +X,-X,+Y,-Y,+Z,-Z, row 0 = t 0;
+ * channels 3 or 4; is_fp16 selects half vs float texels (stored as RGBA16F, like the
+ * reference's GL_RGB16F faces). NULL clears the skybox.                              */
+rt_status rt_set_skybox(rt_context* ctx, const void* faces, int face_size,
+                        int channels, int is_fp16);
+
+/* Replaces InitBlueNoiseTex (src/ForwardShadingPipeline.cpp:39-49): GL_R8, REPEAT,
+ * bilinear. NULL => every fetch returns (0,0,0,1) ("as shipped": the texture is
+ * mip-incomplete and its sampler unit is never assigned).               */
+rt_status rt_set_noise(rt_context* ctx, const unsigned char* r8, int w, int h);
+
+/* Replaces glDispatchCompute + glMemoryBarrier (src/ForwardShadingPipeline.cpp:175-180).
+ * Outputs are DEVICE pointers to full-frame (width x height) row-major buffers; only
+ * rows [row_begin,row_end) are written. d_color / d_position: RGBA32F (outputImage /
+ * gPosition, glsl:61-62). d_normal: RGBA16F (gNormal, glsl:63) or RGBA32F with
+ * RT_FLAG_NORMAL_FP32. d_object_id: optional int32 per pixel (last-hit object index,
+ * -1 on a primary miss), may be NULL. Any of the three image pointers may be NULL to
+ * skip that store. The pointers may be peer-mapped (NVLink) addresses.
+ * Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the legacy default stream). */
+rt_status rt_render(rt_context* ctx, const rt_frame_params* params,
+                    float* d_color_rgba32f, float* d_position_rgba32f,
+                    void* d_normal, int32_t* d_object_id, void* cuda_stream);
+
+/* One whole reference frame through HOST buffers, as ForwardShadingPipline::Render does
+ * it (SSBO upload every frame, dispatch, read-back): scene H2D + render + D2H of the
+ * rendered rows into pinned or pageable host buffers. objects/lights may be NULL to
+ * reuse the last upload. Synchronous.                                              */
+rt_status rt_render_host(rt_context* ctx, const rt_frame_params* params,
+                         const void* objects, int n, const void* lights, int m,
+                         float* h_color_rgba32f, float* h_position_rgba32f,
+                         void* h_normal, int32_t* h_object_id);
+
+/* Replaces the profiler's glFinish (src/PerformanceProfiler.cpp:49-65). */
+rt_status rt_synchronize(rt_context* ctx);
+
+/* CUDA-GL interop variant writing into the app's GL textures. No GL stack exists on
+ * the build or GPU machines: always RT_ERR_UNAVAILABLE here.                       */
+rt_status rt_render_gl(rt_context* ctx, const rt_frame_params* params,
+                       unsigned gl_tex_color, unsigned gl_tex_position, unsigned gl_tex_normal);
+
+/* Counters accumulated by renders that carried RT_FLAG_COUNTERS since the last reset.
+ * out must hold RT_CNT_COUNT uint64 values. Synchronises the context's device.     */
+rt_status rt_get_counters(rt_context* ctx, uint64_t* out, int reset);
+
+/* Pinned host memory helpers for the e2e path (cudaHostAlloc / cudaFreeHost). */
+rt_status rt_host_alloc(void** out, size_t bytes);
+rt_status rt_host_free(void* p);
+
+/* Measurement helper: runs an FMA-only micro-kernel and returns the measured FP32
+ * peak in TFLOP/s (the roofline denominator MEASURED_PEAKS.json lacks) and the SM
+ * count. Not on the render path.                                                  */
+rt_status rt_measure_fp32_peak(rt_context* ctx, double* tflops, int* sm_count, double* ms);
+
+/* Device kernel launch counter (every kernel this library launched on ctx). */
+uint64_t  rt_launch_count(rt_context* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_ABI_H_ */

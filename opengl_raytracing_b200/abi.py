@@ -1,0 +1,105 @@
+"""ctypes binding of librt_b200.so (include/rt_abi.h) — the reference-side stub.
+
+This is the Python spelling of the binding INTEGRATION.md shows for the C++ host: every
+function below is one ``extern "C"`` entry point. There is no fallback: if the CUDA
+library is missing or fails to load, importing callers get ``RtLibraryError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "librt_b200.so")
+
+RT_OK, RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NCCL, RT_ERR_OOM, RT_ERR_UNAVAILABLE = range(6)
+
+FLAG_NORMAL_FP32 = 0x01
+FLAG_PARITY_MATH = 0x02
+FLAG_SKYBOX_HW = 0x04
+FLAG_COUNTERS = 0x08
+FLAG_ACCUMULATE = 0x10
+FLAG_NO_REGROUP = 0x20
+
+COUNTER_NAMES = [
+    "rays", "aabb", "sphere", "plane_early", "plane_full", "hit_update_sphere", "hit_update_plane",
+    "light_point", "light_dir", "light_area", "pbr", "pcf_setup", "pcf_sample", "pcss_probe",
+    "sss_sample", "bounce_mirror", "bounce_refract", "bounce_diffuse", "rr", "camera", "miss",
+]
+RT_CNT_COUNT = len(COUNTER_NAMES)
+
+EXPORTED_SYMBOLS = [
+    "rt_abi_version", "rt_status_string", "rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene",
+    "rt_set_skybox", "rt_set_noise", "rt_render", "rt_render_host", "rt_synchronize", "rt_render_gl",
+    "rt_get_counters", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
+]
+
+
+class RtLibraryError(RuntimeError):
+    pass
+
+
+class RtError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"rt_status {status}: {msg}")
+        self.status = status
+
+
+class FrameParams(C.Structure):
+    """rt_frame_params (include/rt_abi.h) == the shader's uniforms, glsl:72-89."""
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32),
+        ("row_begin", C.c_int32), ("row_end", C.c_int32),
+        ("num_objects", C.c_int32), ("num_lights", C.c_int32),
+        ("camera_pos", C.c_float * 3), ("camera_dir", C.c_float * 3),
+        ("camera_up", C.c_float * 3), ("camera_right", C.c_float * 3),
+        ("fov_deg", C.c_float), ("focal_length", C.c_float), ("max_ray_distance", C.c_float),
+        ("use_skybox", C.c_int32),
+        ("noise_scale", C.c_float * 2),
+        ("frame_count", C.c_int32), ("num_samples", C.c_int32), ("max_ray_depth", C.c_int32),
+        ("flags", C.c_uint32),
+    ]
+
+
+_lib = None
+
+
+def load_library(path: str | None = None) -> C.CDLL:
+    """dlopen librt_b200.so and declare every prototype. Fails loudly."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.isfile(p):
+        raise RtLibraryError(
+            f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback.")
+    try:
+        lib = C.CDLL(p, mode=C.RTLD_GLOBAL)
+    except OSError as e:  # missing libcudart etc.
+        raise RtLibraryError(f"cannot load {p}: {e}") from e
+    vp, ip = C.c_void_p, C.c_int
+    lib.rt_abi_version.restype = ip
+    lib.rt_status_string.restype = C.c_char_p
+    lib.rt_status_string.argtypes = [ip]
+    lib.rt_create.argtypes = [C.POINTER(vp), ip]
+    lib.rt_destroy.argtypes = [vp]
+    lib.rt_destroy.restype = None
+    lib.rt_last_error.argtypes = [vp]
+    lib.rt_last_error.restype = C.c_char_p
+    lib.rt_upload_scene.argtypes = [vp, vp, ip, vp, ip, vp, ip]
+    lib.rt_set_skybox.argtypes = [vp, vp, ip, ip, ip]
+    lib.rt_set_noise.argtypes = [vp, vp, ip, ip]
+    lib.rt_render.argtypes = [vp, C.POINTER(FrameParams), vp, vp, vp, vp, vp]
+    lib.rt_render_host.argtypes = [vp, C.POINTER(FrameParams), vp, ip, vp, ip, vp, vp, vp, vp]
+    lib.rt_synchronize.argtypes = [vp]
+    lib.rt_render_gl.argtypes = [vp, C.POINTER(FrameParams), C.c_uint, C.c_uint, C.c_uint]
+    lib.rt_get_counters.argtypes = [vp, C.POINTER(C.c_uint64), ip]
+    lib.rt_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    lib.rt_host_free.argtypes = [vp]
+    lib.rt_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(ip), C.POINTER(C.c_double)]
+    lib.rt_launch_count.argtypes = [vp]
+    lib.rt_launch_count.restype = C.c_uint64
+    if path is None:
+        _lib = lib
+    return lib

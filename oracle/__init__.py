@@ -1,0 +1,124 @@
+"""oracle — TEST INFRASTRUCTURE. CPU checkers for the ray-tracing pass.
+
+Two shared libraries export the same C API (oracle_api.h):
+  * ``port``      oracle/librt_oracle.so      — rt_oracle.cpp, this repo's CPU restatement
+  * ``reference`` oracle/_ref/libref_shader.so — the reference's own GLSL compiled as C++
+                                                 (make_ref.py; needs /root/reference to BUILD,
+                                                 not to run)
+Only tests/, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline legs may import this
+package. The product (opengl_raytracing_b200) never does and has no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from opengl_raytracing_b200 import abi
+from opengl_raytracing_b200.pipeline import workload_params
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "librt_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libref_shader.so")
+REFERENCE_ROOT = "/root/reference"
+
+_libs: dict = {}
+
+
+def build_port(force: bool = False) -> str:
+    src = os.path.join(HERE, "rt_oracle.cpp")
+    deps = [src, os.path.join(HERE, "oracle_api.h"), os.path.join(HERE, "..", "include", "rt_abi.h")]
+    if not force and os.path.isfile(PORT_SO) and all(os.path.getmtime(PORT_SO) >= os.path.getmtime(d) for d in deps):
+        return PORT_SO
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-fno-fast-math", "-fPIC",
+                    "-shared", "-Wall", "-o", PORT_SO, src], check=True)
+    _libs.pop("port", None)
+    return PORT_SO
+
+
+def build_ref(force: bool = False) -> str | None:
+    """Builds oracle/_ref from /root/reference when that tree is present (this container);
+    on the GPU box the prebuilt .so that travelled with the snapshot is used as is."""
+    from . import make_ref
+    if not os.path.isfile(make_ref.REF_SHADER):
+        return REF_SO if os.path.isfile(REF_SO) else None
+    deps = [make_ref.REF_SHADER, os.path.join(HERE, "ref_harness.cpp"), os.path.join(HERE, "glsl_shim.h"),
+            os.path.join(HERE, "make_ref.py")]
+    if not force and os.path.isfile(REF_SO) and all(os.path.getmtime(REF_SO) >= os.path.getmtime(d) for d in deps):
+        return REF_SO
+    make_ref.build()
+    _libs.pop("reference", None)
+    return REF_SO
+
+
+def have(kind: str) -> bool:
+    return os.path.isfile(PORT_SO if kind == "port" else REF_SO)
+
+
+def load(kind: str = "port") -> C.CDLL:
+    if kind in _libs:
+        return _libs[kind]
+    path = PORT_SO if kind == "port" else REF_SO
+    if kind == "port" and not os.path.isfile(path):
+        build_port()
+    lib = C.CDLL(path)
+    lib.oracle_kind.restype = C.c_char_p
+    vp, ip = C.c_void_p, C.c_int
+    lib.oracle_render.argtypes = [C.POINTER(abi.FrameParams), vp, vp, vp, ip, vp, ip, ip,
+                                  ip, ip, ip, ip, ip, ip, vp, vp, vp, vp, ip]
+    lib.oracle_render.restype = ip
+    assert lib.oracle_kind().decode() == kind
+    _libs[kind] = lib
+    return lib
+
+
+_sky_cache: dict = {}
+
+
+def _sky_f32(sky: np.ndarray | None):
+    """(6,S,S,3|4) fp16/fp32 faces -> RGBA32F holding FP16-rounded values (what the GL_RGB16F
+    cube map of src/TextureLoader.cpp:143 stores)."""
+    if sky is None:
+        return None
+    key = id(sky)
+    if key not in _sky_cache:
+        s = sky.astype(np.float16).astype(np.float32)
+        if s.shape[-1] == 3:
+            s = np.concatenate([s, np.ones(s.shape[:-1] + (1,), np.float32)], axis=-1)
+        _sky_cache.clear()
+        _sky_cache[key] = np.ascontiguousarray(s)
+    return _sky_cache[key]
+
+
+def render(w, kind: str = "port", x0: int = 0, y0: int = 0, sx: int = 1, sy: int = 1,
+           nx: int | None = None, ny: int | None = None, threads: int = 0, params: abi.FrameParams | None = None):
+    """Runs one of the CPU oracles on a ``synthetic.Workload``. Renders pixels
+    (x0+i*sx, y0+j*sy); default = the full frame. Returns a dict of (ny,nx,4) float32 arrays
+    ``color``/``position``/``normal`` (row 0 = gl y 0) and ``counters``."""
+    lib = load(kind)
+    p = params or workload_params(w)
+    if nx is None:
+        nx = (p.width - x0 + sx - 1) // sx
+    if ny is None:
+        ny = (p.height - y0 + sy - 1) // sy
+    color = np.zeros((ny, nx, 4), np.float32)
+    position = np.zeros((ny, nx, 4), np.float32)
+    normal = np.zeros((ny, nx, 4), np.float32)
+    counters = (C.c_uint64 * abi.RT_CNT_COUNT)()
+    objects = np.ascontiguousarray(w.objects)
+    lights = np.ascontiguousarray(w.lights)
+    sky = _sky_f32(w.skybox) if w.use_skybox else None
+    noise = None if w.noise is None else np.ascontiguousarray(w.noise, dtype=np.uint8)
+    rc = lib.oracle_render(
+        C.byref(p), objects.ctypes.data, lights.ctypes.data,
+        None if sky is None else sky.ctypes.data, 0 if sky is None else sky.shape[1],
+        None if noise is None else noise.ctypes.data,
+        0 if noise is None else noise.shape[1], 0 if noise is None else noise.shape[0],
+        x0, y0, sx, sy, nx, ny, color.ctypes.data, position.ctypes.data, normal.ctypes.data,
+        C.cast(counters, C.c_void_p), threads)
+    if rc != 0:
+        raise RuntimeError(f"oracle_render({kind}) failed: {rc}")
+    return {"color": color, "position": position, "normal": normal,
+            "counters": {k: int(counters[i]) for i, k in enumerate(abi.COUNTER_NAMES)}}
