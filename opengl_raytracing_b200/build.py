@@ -1,0 +1,59 @@
+"""nvcc build of csrc/ -> csrc/librt_b200.so for sm_100a (in-tree, so the .so travels to
+the GPU box). Two builds of the kernel TU (RT_FLAG_PARITY_MATH selects at run time), BOTH with
+-fmad=false: the geometric chain (ray -> t -> P -> N -> next ray) must round exactly like the
+shader's unfused arithmetic or mirror/glass paths diverge after a bounce. The fast build fuses
+explicitly (fmaf) and uses SFU approximations only in colour-only shading code."""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(CSRC, "librt_b200.so")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-Xptxas", "-v"]
+UNITS = [  # (source, extra flags)
+    ("rt_kernel_fast.cu", ["-fmad=false"]),
+    ("rt_kernel_parity.cu", ["-fmad=false"]),
+    ("rt_abi.cu", []),
+    ("rt_peak.cu", []),
+]
+HEADERS = ["rt_kernel.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h")]
+
+
+def _stale(target: str, deps: list) -> bool:
+    if not os.path.isfile(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
+    objs, rebuilt = [], False
+    for src, extra in UNITS:
+        s = os.path.join(CSRC, src)
+        o = s[:-3] + ".o"
+        objs.append(o)
+        if force or _stale(o, [s] + hdrs):
+            cmd = [NVCC] + ARCH + COMMON + extra + ["-c", s, "-o", o]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            with open(o + ".log", "w") as f:
+                f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+            if verbose or r.returncode != 0:
+                sys.stderr.write(r.stdout + r.stderr)
+            if r.returncode != 0:
+                raise RuntimeError(f"nvcc failed on {src}")
+            rebuilt = True
+    if force or rebuilt or _stale(LIB, objs):
+        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs
+        subprocess.run(cmd, check=True)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="-f" in sys.argv, verbose="-v" in sys.argv))

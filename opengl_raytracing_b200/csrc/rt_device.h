@@ -1,0 +1,66 @@
+// rt_device.h — types shared by the host side of the C ABI (rt_abi.cu) and the sm_100a
+// kernels (rt_kernel.cuh). Not a public header.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/rt_abi.h"
+
+namespace rt {
+
+// Device-resident scene in the layout the kernel stages into shared memory. Built on the
+// host by stage_scene() from the std430 Object[]/Light[] bytes (rt_upload_scene); every
+// derived value is computed with the same FP32 operations the shader would use per call,
+// so hoisting it is value-exact.
+//
+//   isect[3*i+0] = (bounds.min.xyz, type bits)         intersectAABB operands (glsl:91-103)
+//   isect[3*i+1] = (bounds.max.xyz, plane slot bits)
+//   isect[3*i+2] = sphere: (position.xyz, radius*radius)   (glsl:106-109)
+//                  plane : (position.xyz, 0)
+//   plane[3*k+0] = (normal.xyz,  size.x/2)              intersectPlane operands (glsl:121-146)
+//   plane[3*k+1] = (right.xyz,   size.y/2)              frame of glsl:130-138, hoisted
+//   plane[3*k+2] = (forward.xyz, 0)
+//   material[4*i..] = (albedo.rgb, metallic) (roughness, diffuseStrength, ior, transparency)
+//                     (subsurfaceColor.rgb, subsurfaceScatter) (scatterDistance, 0, 0, 0)
+//   lights[6*j..]   = the raw 96-byte Light record
+struct DeviceScene {
+  const float4* isect;
+  const float4* plane;
+  const float4* material;
+  const float4* lights;
+  int num_objects;
+  int num_planes;
+  int num_lights;
+  int scene_in_smem;         // 1: isect/plane/lights fit the shared-memory budget
+  const uint2* sky;          // 6 * size * size RGBA16F texels (manual FP32 bilinear path)
+  unsigned long long sky_tex;  // cudaTextureObject_t cubemap (RT_FLAG_SKYBOX_HW)
+  int sky_size;
+  const unsigned char* noise;  // R8
+  int noise_w, noise_h;
+};
+
+struct KernelParams {
+  rt_frame_params fp;
+  float tan_fov;             // tan(radians(fov) * 0.5), evaluated on the host (uniform)
+  float aspect;
+  DeviceScene sc;
+  float4* color;
+  float4* position;
+  void* normal;
+  int* object_id;
+  unsigned* tile_counter;    // monotonically increasing work counter (never reset)
+  unsigned tile_base;        // value of the counter when this launch started
+  unsigned tiles_x, tiles_y;
+  unsigned long long* counters;   // RT_CNT_COUNT reference-literal op counters
+};
+
+size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights);
+
+// One launcher per (variant) translation unit: rt_kernel_fast.cu is compiled with FMA
+// contraction, rt_kernel_parity.cu with -fmad=false and IEEE-only arithmetic.
+cudaError_t launch_render_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
+cudaError_t launch_render_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
+
+cudaError_t upload_tables_fast(const float* halton2, const float* halton3);     // 64 entries each
+cudaError_t upload_tables_parity(const float* halton2, const float* halton3);
+
+}  // namespace rt

@@ -1,0 +1,14 @@
+// rt_kernel_parity.cu — the "parity" build of the ray-tracing kernel (see rt_kernel.cuh).
+// Compiled with -fmad=false: no FMA contraction, IEEE division and square root everywhere.
+#define RT_PARITY 1
+#define RT_VARIANT_NS parity
+#include "rt_kernel.cuh"
+
+namespace rt {
+cudaError_t launch_render_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+  return parity::launch_render(kp, sm_count, stream, warps_launched);
+}
+cudaError_t upload_tables_parity(const float* halton2, const float* halton3) {
+  return parity::upload_tables(halton2, halton3);
+}
+}  // namespace rt

@@ -267,3 +267,34 @@ class ForwardShadingPipeline:
         if self.taaEnabled:
             self.frameCount += 1
         return self.outputTex, self.gPositionTex, self.gNormalTex
+
+
+# --------------------------------------------------------------------------- convenience
+def bind_workload(ctx: RtContext, w) -> None:
+    """Upload a ``synthetic.Workload``'s scene, skybox and noise (what Init + the first
+    ssbo.update() do in the reference)."""
+    ctx.upload_scene(w.objects, w.lights)
+    ctx.set_skybox(w.skybox if w.use_skybox else None)
+    ctx.set_noise(w.noise)
+
+
+def render_workload(ctx: RtContext, w, flags: int = 0, params: abi.FrameParams | None = None, bind: bool = True):
+    """Render a workload into fresh device buffers and return host copies:
+    dict(color (H,W,4) f32, position (H,W,4) f32, normal (H,W,4) f32 — from the RGBA16F image
+    unless FLAG_NORMAL_FP32 —, object_id (H,W) i32). Row 0 = gl y 0."""
+    import torch
+    if bind:
+        bind_workload(ctx, w)
+    p = params or workload_params(w, flags=flags)
+    dev = f"cuda:{ctx.device}"
+    H, W = p.height, p.width
+    color = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
+    position = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
+    ndt = torch.float32 if (p.flags & abi.FLAG_NORMAL_FP32) else torch.float16
+    normal = torch.zeros(H, W, 4, dtype=ndt, device=dev)
+    oid = torch.full((H, W), -3, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(ctx.device).cuda_stream
+    ctx.render(p, color, position, normal, oid, stream)
+    torch.cuda.synchronize(ctx.device)
+    return {"color": color.cpu().numpy(), "position": position.cpu().numpy(),
+            "normal": normal.float().cpu().numpy(), "object_id": oid.cpu().numpy()}

@@ -237,8 +237,12 @@ def parse_scene(text: str) -> Scene:
             lights.append(l)
             lnames.append(name)
     sc = Scene()
-    sc.objects = np.concatenate(objs) if objs else new_objects(0)
-    sc.lights = np.concatenate(lights) if lights else new_lights(0)
+    sc.objects = new_objects(len(objs))      # (np.concatenate would drop the std430 padding)
+    for i, o in enumerate(objs):
+        sc.objects[i] = o[0]
+    sc.lights = new_lights(len(lights))
+    for i, l in enumerate(lights):
+        sc.lights[i] = l[0]
     sc.object_names, sc.light_names = onames, lnames
     return sc
 

@@ -67,7 +67,7 @@ def load(kind: str = "port") -> C.CDLL:
     lib.oracle_kind.restype = C.c_char_p
     vp, ip = C.c_void_p, C.c_int
     lib.oracle_render.argtypes = [C.POINTER(abi.FrameParams), vp, vp, vp, ip, vp, ip, ip,
-                                  ip, ip, ip, ip, ip, ip, vp, vp, vp, vp, ip]
+                                  ip, ip, ip, ip, ip, ip, vp, vp, vp, vp, vp, ip]
     lib.oracle_render.restype = ip
     assert lib.oracle_kind().decode() == kind
     _libs[kind] = lib
@@ -106,6 +106,7 @@ def render(w, kind: str = "port", x0: int = 0, y0: int = 0, sx: int = 1, sy: int
     color = np.zeros((ny, nx, 4), np.float32)
     position = np.zeros((ny, nx, 4), np.float32)
     normal = np.zeros((ny, nx, 4), np.float32)
+    object_id = np.zeros((ny, nx), np.int32)
     counters = (C.c_uint64 * abi.RT_CNT_COUNT)()
     objects = np.ascontiguousarray(w.objects)
     lights = np.ascontiguousarray(w.lights)
@@ -116,9 +117,9 @@ def render(w, kind: str = "port", x0: int = 0, y0: int = 0, sx: int = 1, sy: int
         None if sky is None else sky.ctypes.data, 0 if sky is None else sky.shape[1],
         None if noise is None else noise.ctypes.data,
         0 if noise is None else noise.shape[1], 0 if noise is None else noise.shape[0],
-        x0, y0, sx, sy, nx, ny, color.ctypes.data, position.ctypes.data, normal.ctypes.data,
+        x0, y0, sx, sy, nx, ny, color.ctypes.data, position.ctypes.data, normal.ctypes.data, object_id.ctypes.data,
         C.cast(counters, C.c_void_p), threads)
     if rc != 0:
         raise RuntimeError(f"oracle_render({kind}) failed: {rc}")
-    return {"color": color, "position": position, "normal": normal,
+    return {"color": color, "position": position, "normal": normal, "object_id": object_id,
             "counters": {k: int(counters[i]) for i, k in enumerate(abi.COUNTER_NAMES)}}

@@ -19,6 +19,8 @@ const char* oracle_kind(void);
 //   noise_r8    : noise_w x noise_h bytes, or NULL => texel (0,0,0,1)
 //   colour      : mean over p->num_samples frames (sequential FP32 sum, then * 1/n);
 //                 position/normal come from the first sample.
+//   object_id   : nx*ny int32, index of the last-hit object (-1 = primary miss), or NULL.
+//                 (_ref writes -2: the shader has no such output.)
 //   counters    : RT_CNT_COUNT reference-literal op counters summed over all rendered
 //                 pixels and samples, or NULL. (_ref returns zeros: it is uninstrumented.)
 //   nthreads    : OpenMP threads, <= 0 => all.
@@ -27,7 +29,7 @@ int oracle_render(const rt_frame_params* p, const void* objects, const void* lig
                   const float* sky_rgba32f, int face_size,
                   const unsigned char* noise_r8, int noise_w, int noise_h,
                   int x0, int y0, int sx, int sy, int nx, int ny,
-                  float* color, float* position, float* normal,
+                  float* color, float* position, float* normal, int32_t* object_id,
                   uint64_t* counters, int nthreads);
 
 #ifdef __cplusplus

@@ -28,7 +28,7 @@ extern "C" int oracle_render(const rt_frame_params* p, const void* objects_, con
                              const float* sky_rgba32f, int face_size,
                              const unsigned char* noise_r8, int noise_w, int noise_h,
                              int x0, int y0, int sx, int sy, int nx, int ny,
-                             float* color, float* position, float* normal,
+                             float* color, float* position, float* normal, int32_t* object_id,
                              uint64_t* counters, int nthreads) {
   if (!p || !color || !position || !normal) return 1;
   const rt_object* ro = (const rt_object*)objects_;
@@ -71,6 +71,7 @@ extern "C" int oracle_render(const rt_frame_params* p, const void* objects_, con
   blueNoiseTex.r8 = noise_r8; blueNoiseTex.width = noise_w; blueNoiseTex.height = noise_h;
   if (counters) for (int k = 0; k < RT_CNT_COUNT; ++k) counters[k] = 0;   // _ref carries no counters
 
+  if (object_id) for (size_t o = 0; o < (size_t)nx * ny; ++o) object_id[o] = -2;
   const int ns = p->num_samples > 0 ? p->num_samples : 1;
   if (nthreads <= 0) nthreads = omp_get_max_threads();
   for (int s = 0; s < ns; ++s) {

@@ -503,7 +503,7 @@ extern "C" int oracle_render(const rt_frame_params* p, const void* objects, cons
                              const float* sky_rgba32f, int face_size,
                              const unsigned char* noise_r8, int noise_w, int noise_h,
                              int x0, int y0, int sx, int sy, int nx, int ny,
-                             float* color, float* position, float* normal,
+                             float* color, float* position, float* normal, int32_t* object_id,
                              uint64_t* counters, int nthreads) {
   if (!p || !color || !position || !normal) return 1;
   Bindings b;
@@ -534,6 +534,7 @@ extern "C" int oracle_render(const rt_frame_params* p, const void* objects, cons
           if (s == 0) {
             for (int c = 0; c < 3; ++c) { color[at + c] = o.color[c]; position[at + c] = o.P[c]; normal[at + c] = o.N[c]; }
             color[at + 3] = 1.0f; position[at + 3] = 1.0f; normal[at + 3] = 1.0f;
+            if (object_id) object_id[(size_t)j * nx + i] = o.objectId;
           } else {
             for (int c = 0; c < 3; ++c) color[at + c] = color[at + c] + o.color[c];
           }

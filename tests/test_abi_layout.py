@@ -1,0 +1,89 @@
+"""C-ABI library: loads and exports every symbol include/rt_abi.h declares; the ctypes
+structures match the header's byte layouts. No compute calls (runs without a GPU)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from opengl_raytracing_b200 import abi, scene as S
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "rt_abi.h")
+
+
+def _declared_functions():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", text)
+    return sorted(set(names))
+
+
+def test_header_functions_match_binding_list():
+    assert _declared_functions() == sorted(abi.EXPORTED_SYMBOLS)
+
+
+def test_library_loads_and_exports_every_symbol():
+    from opengl_raytracing_b200 import build
+    build.build()
+    lib = abi.load_library()
+    for name in _declared_functions():
+        assert hasattr(lib, name), name
+    assert lib.rt_abi_version() == 1
+    assert lib.rt_status_string(5) == b"RT_ERR_UNAVAILABLE"
+
+
+def test_struct_layouts_against_c_compiler(tmp_path):
+    """sizeof/offsetof from gcc on the header == numpy dtypes == ctypes FrameParams."""
+    src = tmp_path / "probe.c"
+    fields = [("rt_object", f) for f in ("type", "position", "radius", "normal", "size", "material", "bounds")]
+    fields += [("rt_material", f) for f in ("albedo", "metallic", "roughness", "diffuseStrength", "ior", "transparency",
+                                             "specular", "subsurfaceScatter", "subsurfaceColor", "scatterDistance")]
+    fields += [("rt_light", f) for f in ("position", "direction", "color", "intensity", "radius", "samples",
+                                          "shadowSoftness", "shadowType", "pcfSamples", "lightSize", "angularRadius")]
+    fields += [("rt_frame_params", f) for f in ("row_begin", "camera_pos", "fov_deg", "use_skybox", "noise_scale",
+                                                 "frame_count", "num_samples", "max_ray_depth", "flags")]
+    body = "".join(f'printf("{s}.{f} %zu\\n", offsetof({s}, {f}));\n' for s, f in fields)
+    body += "".join(f'printf("sizeof.{s} %zu\\n", sizeof({s}));\n' for s in ("rt_object", "rt_material", "rt_light", "rt_aabb", "rt_frame_params"))
+    src.write_text(f'#include <stdio.h>\n#include "{HEADER}"\nint main(void){{\n{body}return 0;}}\n')
+    exe = tmp_path / "probe"
+    subprocess.run(["gcc", "-std=c11", str(src), "-o", str(exe)], check=True)
+    out = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    assert int(out["sizeof.rt_object"]) == 176 == S.OBJECT_DTYPE.itemsize
+    assert int(out["sizeof.rt_material"]) == 80 == S.MATERIAL_DTYPE.itemsize
+    assert int(out["sizeof.rt_light"]) == 96 == S.LIGHT_DTYPE.itemsize
+    assert int(out["sizeof.rt_aabb"]) == 32 == S.AABB_DTYPE.itemsize
+    assert int(out["sizeof.rt_frame_params"]) == C.sizeof(abi.FrameParams)
+    for dt, name in ((S.OBJECT_DTYPE, "rt_object"), (S.MATERIAL_DTYPE, "rt_material"), (S.LIGHT_DTYPE, "rt_light")):
+        for f in dt.names:
+            key = f"{name}.{f}"
+            if key in out:
+                assert dt.fields[f][1] == int(out[key]), key
+    for f in ("row_begin", "camera_pos", "fov_deg", "use_skybox", "noise_scale", "frame_count", "num_samples", "max_ray_depth", "flags"):
+        assert getattr(abi.FrameParams, f).offset == int(out[f"rt_frame_params.{f}"]), f
+    # the survey's measured std430 offsets
+    assert S.OBJECT_DTYPE.fields["material"][1] == 64 and S.OBJECT_DTYPE.fields["bounds"][1] == 144
+    assert S.MATERIAL_DTYPE.fields["subsurfaceColor"][1] == 64 and S.LIGHT_DTYPE.fields["shadowSoftness"][1] == 72
+
+
+def test_no_cpu_fallback_without_gpu():
+    """Without a CUDA device rt_create must fail loudly (RT_ERR_UNAVAILABLE), never render."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from opengl_raytracing_b200.pipeline import RtContext
+    with pytest.raises(abi.RtError) as ei:
+        RtContext(0)
+    assert ei.value.status == abi.RT_ERR_UNAVAILABLE
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "opengl_raytracing_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, fn), encoding="utf-8", errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), fn
+                assert "oracle/" not in text and "oracle_api" not in text and "librt_oracle" not in text, fn
