@@ -1,0 +1,385 @@
+#!/usr/bin/env python3
+"""bench.py — Mrays/s of the ray-tracing pass on BASELINE.json's metric config.
+
+  python bench.py --gpus N --steps K --warmup W            (this repo's CUDA path)
+  python bench.py --impl reference --gpus N --steps K ...  (the reference's CPU path)
+
+A "step" is one pass of the hot path over one frame of synthetic input. At N=1 the workload
+is BASELINE.json configs[1] (C2: default scene, 1920x1080, PBR + PCSS area light + skybox,
+depth 3, 1 spp). ``value`` is whole-job Mrays/s with inputs resident in HBM (CUDA events on
+the launching stream, max over ranks); ``e2e`` is the same metric through the reference-facing
+C-ABI call rt_render_host with HOST buffers (scene H2D + render + D2H of the three images
+inside the timed region). 1 ray = 1 intersectObjects call of the reference-literal
+algorithm, counted by the kernel's counter variant (validated against the oracle in
+tests/test_parity_gpu.py::test_counters_match_oracle).
+
+N > 1 (torchrun, one rank per GPU): sample-range sharding — every rank renders one
+full frame at its own frameCount, the partial colours are summed on rank 0 with one NCCL
+reduce inside the timed region: per-GPU work is fixed ("weak"). ``--shard rows`` gives the
+strong-scaling row-tile variant (no collective in the data path, tiles gathered to rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s"
+
+# flop model v0: reference-literal flops per counted operation, (flops, SFU ops)
+FLOP_MODEL = {
+    "rays": (3, 3), "aabb": (25, 0), "sphere": (32, 2), "plane_early": (17, 1), "plane_full": (80, 3),
+    "hit_update_sphere": (18, 1), "hit_update_plane": (0, 0),
+    "light_point": (57, 3), "light_dir": (45, 2), "light_area": (69, 4), "pbr": (101, 4),
+    "pcf_setup": (32, 1), "pcf_sample": (56, 3), "pcss_probe": (36, 2), "sss_sample": (82, 7),
+    "bounce_mirror": (66, 2), "bounce_refract": (129, 5), "bounce_diffuse": (152, 9),
+    "rr": (25, 3), "camera": (40, 2), "miss": (40, 1),
+}
+
+
+def algorithmic_flops(counters: dict) -> tuple:
+    f = sum(counters[k] * v[0] for k, v in FLOP_MODEL.items())
+    s = sum(counters[k] * v[1] for k, v in FLOP_MODEL.items())
+    return f, s
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--config", type=int, default=2, help="BASELINE.json config number (1..5); the metric is quoted on 2")
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--samples", type=int, default=None, help="override num_samples (config 4 defaults to 64)")
+    ap.add_argument("--shard", choices=["samples", "rows"], default="samples")
+    ap.add_argument("--flags", type=lambda s: int(s, 0), default=0, help="extra RT_FLAG_* bits (e.g. 0x2 parity math)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-step", type=int, default=0, help="oracle pixel stride for the CPU baseline (0 = auto)")
+    return ap.parse_args()
+
+
+def workload_for(args):
+    from opengl_raytracing_b200 import synthetic
+    w = synthetic.config(args.config, args.width, args.height)
+    if args.samples is not None:
+        w.num_samples = args.samples
+    return w
+
+
+class ClockSampler:
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            "hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+            "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+            "hw_power_brake": getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_baseline(w, kind: str, budget_s: float = 15.0, step: int = 0) -> dict:
+    """Times the CPU implementation of the path (oracle/_ref = the reference's own shader source
+    compiled as C++, else the port) on a bounded pixel subset with all host threads."""
+    import oracle
+    if kind == "reference" and not oracle.have("reference"):
+        kind = "port"
+    if kind == "port":
+        oracle.build_port()
+    cores = os.cpu_count() or 1
+    # calibrate on a sparse subset, then size the timed sample to ~budget_s of CPU work
+    oracle.render(w, kind, x0=0, y0=0, sx=1, sy=1, nx=4, ny=4)      # warm: library load, skybox conversion
+    t0 = time.perf_counter()
+    cal = oracle.render(w, "port", x0=3, y0=5, sx=32, sy=32)
+    t_cal = time.perf_counter() - t0
+    px_cal = cal["color"].shape[0] * cal["color"].shape[1] * max(1, w.num_samples)
+    per_px = t_cal / max(px_cal, 1)
+    total_px = w.width * w.height * max(1, w.num_samples)
+    if step <= 0:
+        step = 1
+        while per_px * total_px / (step * step) > budget_s and step < 64:
+            step *= 2
+    x0, y0 = (3 % step, 5 % step)
+    best, rays = None, 0
+    for _ in range(2):
+        t0 = time.perf_counter()
+        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    rays = oracle.render(w, "port", x0=x0, y0=y0, sx=step, sy=step)["counters"]["rays"]
+    return {"value": rays / best / 1e6, "unit": METRIC, "cores": cores, "kind": kind,
+            "sample": f"{w.name} {w.width}x{w.height}, every {step}-th pixel in x and y (offset {x0},{y0}), "
+                      f"{rays} rays in {best:.3f} s, best of 2, OpenMP dynamic over rows",
+            "seconds": best, "rays": rays, "step": step}
+
+
+def run_reference(args) -> None:
+    """The reference's own CPU implementation of the path on the box's host cores: one step =
+    one bounded sample of the same frame. Only rank 0 works."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    w = workload_for(args)
+    kind = "reference" if oracle.have("reference") else "port"
+    base = cpu_baseline(w, kind, budget_s=6.0, step=args.cpu_sample_step)
+    step, x0, y0 = base["step"], 3 % base["step"], 5 % base["step"]
+    for _ in range(max(0, args.warmup - 1)):
+        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step)
+    dt = (time.perf_counter() - t0) / max(1, args.steps)
+    val = base["rays"] / dt / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{w.name}: {w.description}", "width": w.width, "height": w.height,
+                   "max_ray_depth": w.max_ray_depth, "num_samples": w.num_samples,
+                   "note": "reference shader source compiled as C++ on host cores; GL/llvmpipe unavailable on this box"},
+        "cpu_baseline": {"value": val, "unit": METRIC, "cores": base["cores"], "kind": base["kind"], "sample": base["sample"]},
+        "e2e": {"value": val, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args) -> None:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from opengl_raytracing_b200 import abi, sharding
+    from opengl_raytracing_b200.pipeline import RtContext, bind_workload, workload_params
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    w = workload_for(args)
+    ctx = RtContext(local)
+    bind_workload(ctx, w)
+    H, W = w.height, w.width
+    ns = max(1, w.num_samples)
+    flags = args.flags
+
+    # ---- sharding plan
+    if world > 1 and args.shard == "rows":
+        ra, rb = sharding.row_range(H, rank, world)
+        params = workload_params(w, flags=flags, row_begin=ra, row_end=rb)
+        scaling, par = "strong", f"row tiles x{world}, gathered to rank 0"
+    elif world > 1:
+        params = workload_params(w, flags=flags | abi.FLAG_ACCUMULATE, frame_count=w.frame_count + rank * ns)
+        scaling, par = "weak", f"sample ranges x{world} ({ns} spp per rank), NCCL reduce to rank 0"
+    else:
+        params = workload_params(w, flags=flags)
+        scaling, par = "weak", "single GPU"
+
+    color = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
+    position = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
+    normal = torch.zeros(H, W, 4, dtype=torch.float16, device=dev)
+    write_geom = (world == 1) or args.shard == "rows" or rank == 0
+    stream = torch.cuda.current_stream(dev)
+
+    # ---- reference-literal op counts for THIS rank's work (untimed, counter variant)
+    pc = abi.FrameParams.from_buffer_copy(params)
+    pc.flags = (params.flags | abi.FLAG_COUNTERS) & ~abi.FLAG_ACCUMULATE
+    ctx.counters(reset=True)
+    ctx.render(pc, color, None, None, None, stream.cuda_stream)
+    counters = ctx.counters(reset=True)
+    rays_rank = counters["rays"]
+    flops_rank, sfu_rank = algorithmic_flops(counters)
+
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)   # > 126 MB L2
+
+    def step():
+        if params.flags & abi.FLAG_ACCUMULATE:
+            color.zero_()
+        ctx.render(params, color, position if write_geom else None, normal if write_geom else None, None, stream.cuda_stream)
+        if world > 1 and args.shard == "rows":
+            for buf in (color, position, normal):
+                sharding.gather_rows(buf, H, world)
+        elif world > 1:
+            sharding.reduce_samples(color, ns * world)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    torch.cuda.synchronize(dev)
+    fp32_peak = ctx.measure_fp32_peak()
+    launches0 = ctx.launch_count()
+
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True),
+           torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    sampler.start()
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()                                  # L2 flush between timed iterations (untimed)
+        ev[i][0].record(stream)
+        if params.flags & abi.FLAG_ACCUMULATE:
+            color.zero_()
+        ctx.render(params, color, position if write_geom else None, normal if write_geom else None, None, stream.cuda_stream)
+        ev[i][1].record(stream)
+        if world > 1 and args.shard == "rows":
+            for buf in (color, position, normal):
+                sharding.gather_rows(buf, H, world)
+        elif world > 1:
+            sharding.reduce_samples(color, ns * world)
+        ev[i][2].record(stream)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    launches = ctx.launch_count() - launches0
+    step_ms = sum(a.elapsed_time(c) for a, _, c in ev) / args.steps
+    kern_ms = sum(a.elapsed_time(b) for a, b, _ in ev) / args.steps    # includes the zero_ fill when accumulating
+    t = torch.tensor([step_ms, kern_ms, float(rays_rank), float(flops_rank)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        step_ms, kern_ms = float(tmax[0]), float(tmax[1])
+        rays_total, flops_total = float(tsum[2]), float(tsum[3])
+    else:
+        rays_total, flops_total = float(rays_rank), float(flops_rank)
+    value = rays_total / (step_ms * 1e-3) / 1e6
+
+    # ---- e2e through the C ABI with host buffers (rank-local frame; aggregate over ranks)
+    px = (params.row_end - params.row_begin) * W
+    h = {}
+    for name, nbytes in (("color", px * 16), ("position", px * 16), ("normal", px * 8)):
+        p = abi.C.c_void_p(0)
+        assert ctx.lib.rt_host_alloc(abi.C.byref(p), H * W * (16 if name != "normal" else 8)) == 0
+        h[name] = p
+    objs = np.ascontiguousarray(w.objects); lights = np.ascontiguousarray(w.lights)
+    pe = abi.FrameParams.from_buffer_copy(params)
+    pe.flags = params.flags & ~abi.FLAG_ACCUMULATE
+    def e2e_step():
+        st = ctx.lib.rt_render_host(ctx.handle, abi.C.byref(pe), objs.ctypes.data, len(objs), lights.ctypes.data, len(lights),
+                                    h["color"], h["position"], h["normal"], None)
+        assert st == 0, ctx.lib.rt_last_error(ctx.handle)
+    for _ in range(3):
+        e2e_step()
+    if world > 1:
+        dist.barrier()
+    e2e_steps = max(5, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
+    te = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_ms = float(te[0])
+    for p in h.values():
+        ctx.lib.rt_host_free(p)
+    h2d = objs.nbytes + lights.nbytes
+    d2h = px * 40
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        ach_tf = flops_rank / (kern_ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{w.name}: {w.description}", "width": W, "height": H, "objects": len(w.objects),
+                       "lights": len(w.lights), "max_ray_depth": w.max_ray_depth, "num_samples": ns,
+                       "parallelism": par, "l2": "flushed between timed iterations (256 MB fill, untimed)",
+                       "rays_per_frame": rays_rank, "rays_per_pixel": rays_rank / (px * 1.0),
+                       "math": "parity" if (flags & abi.FLAG_PARITY_MATH) else "fast"},
+            "ms_per_frame": kern_ms,
+            "roofline": {"bound": "fp32", "achieved": ach_tf, "peak": fp32_peak["tflops"], "unit": "TFLOP/s",
+                         "frac": ach_tf / fp32_peak["tflops"], "traffic": None,
+                         "peak_source": "measured in this run: FFMA-only micro-kernel (rt_measure_fp32_peak); "
+                                        "MEASURED_PEAKS.json has no FP32 entry",
+                         "algorithmic_flops_per_launch": flops_rank, "algorithmic_sfu_ops_per_launch": sfu_rank,
+                         "flop_model": "v0 (SURVEY.md 8d), reference-literal op counts x fixed constants",
+                         "hbm_write": {"bytes_per_launch": px * 40, "achieved_gbs": px * 40 / (kern_ms * 1e-3) / 1e9,
+                                       "peak_gbs": peaks.get("hbm_gbs"), "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)"}},
+            "e2e": {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": METRIC, "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "call": "rt_render_host: scene H2D (pinned staging) + rt_render + D2H of colour/position/normal into pinned host buffers"},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "wall_s_timed_region": t_wall,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            import oracle
+            kind = "reference" if oracle.have("reference") else "port"
+            cb = cpu_baseline(w, kind, budget_s=12.0, step=args.cpu_sample_step)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
