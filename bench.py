@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--samples", type=int, default=None, help="override num_samples (config 4 defaults to 64)")
     ap.add_argument("--shard", choices=["samples", "rows"], default="samples")
     ap.add_argument("--flags", type=lambda s: int(s, 0), default=0, help="extra RT_FLAG_* bits (e.g. 0x2 parity math)")
+    ap.add_argument("--host-path", type=int, default=0, help="rt_set_host_path: 0 auto, 1 staged, 2 banded, 3 zero-copy")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-step", type=int, default=0, help="oracle pixel stride for the CPU baseline (0 = auto)")
     return ap.parse_args()
@@ -308,6 +309,7 @@ def run_ours(args) -> None:
     objs = np.ascontiguousarray(w.objects); lights = np.ascontiguousarray(w.lights)
     pe = abi.FrameParams.from_buffer_copy(params)
     pe.flags = params.flags & ~abi.FLAG_ACCUMULATE
+    assert ctx.lib.rt_set_host_path(ctx.handle, args.host_path) == 0
     def e2e_step():
         st = ctx.lib.rt_render_host(ctx.handle, abi.C.byref(pe), objs.ctypes.data, len(objs), lights.ctypes.data, len(lights),
                                     h["color"], h["position"], h["normal"], None)

@@ -123,7 +123,7 @@ typedef enum rt_status {
 #define RT_FLAG_SKYBOX_HW       0x04u /* miss path through the CUDA cubemap texture object (HW filter) */
 #define RT_FLAG_COUNTERS        0x08u /* accumulate the reference-literal op counters (rt_get_counters)*/
 #define RT_FLAG_ACCUMULATE      0x10u /* colour += instead of = (sample-range partial sums) */
-#define RT_FLAG_NO_REGROUP      0x20u /* disable warp-level ray regrouping (A/B measurement only)      */
+#define RT_FLAG_LITERAL_KERNEL  0x20u /* one-ray-per-lane literal kernel instead of the packet kernel   */
 
 /* == the shader's uniforms (shader/raytracingCs.glsl:72-89) + the compile-time constants
  *    promoted to run time (:4 MAX_RAY_DEPTH, image size) + the sharding window.          */
@@ -227,6 +227,11 @@ rt_status rt_render_host(rt_context* ctx, const rt_frame_params* params,
                          const void* objects, int n, const void* lights, int m,
                          float* h_color_rgba32f, float* h_position_rgba32f,
                          void* h_normal, int32_t* h_object_id);
+
+/* How rt_render_host moves the three images to the host (a tuning knob, not semantics):
+ * AUTO = BANDED when every host buffer is pinned (rt_host_alloc / cudaHostRegister), else STAGED. */
+enum { RT_HOST_PATH_AUTO = 0, RT_HOST_PATH_STAGED = 1, RT_HOST_PATH_BANDED = 2, RT_HOST_PATH_ZEROCOPY = 3 };
+rt_status rt_set_host_path(rt_context* ctx, int path);
 
 /* Replaces the profiler's glFinish (src/PerformanceProfiler.cpp:49-65). */
 rt_status rt_synchronize(rt_context* ctx);

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "csrc", "librt_b200.so")   # env: dev A/B builds only
 
 RT_OK, RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NCCL, RT_ERR_OOM, RT_ERR_UNAVAILABLE = range(6)
 
@@ -19,7 +19,8 @@ FLAG_PARITY_MATH = 0x02
 FLAG_SKYBOX_HW = 0x04
 FLAG_COUNTERS = 0x08
 FLAG_ACCUMULATE = 0x10
-FLAG_NO_REGROUP = 0x20
+FLAG_LITERAL_KERNEL = 0x20
+HOST_PATH_AUTO, HOST_PATH_STAGED, HOST_PATH_BANDED, HOST_PATH_ZEROCOPY = range(4)
 
 COUNTER_NAMES = [
     "rays", "aabb", "sphere", "plane_early", "plane_full", "hit_update_sphere", "hit_update_plane",
@@ -31,7 +32,7 @@ RT_CNT_COUNT = len(COUNTER_NAMES)
 EXPORTED_SYMBOLS = [
     "rt_abi_version", "rt_status_string", "rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene",
     "rt_set_skybox", "rt_set_noise", "rt_render", "rt_render_host", "rt_synchronize", "rt_render_gl",
-    "rt_get_counters", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
+    "rt_get_counters", "rt_set_host_path", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
 ]
 
 
@@ -93,6 +94,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_render.argtypes = [vp, C.POINTER(FrameParams), vp, vp, vp, vp, vp]
     lib.rt_render_host.argtypes = [vp, C.POINTER(FrameParams), vp, ip, vp, ip, vp, vp, vp, vp]
     lib.rt_synchronize.argtypes = [vp]
+    lib.rt_set_host_path.argtypes = [vp, ip]
     lib.rt_render_gl.argtypes = [vp, C.POINTER(FrameParams), C.c_uint, C.c_uint, C.c_uint]
     lib.rt_get_counters.argtypes = [vp, C.POINTER(C.c_uint64), ip]
     lib.rt_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]

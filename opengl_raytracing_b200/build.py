@@ -22,7 +22,7 @@ UNITS = [  # (source, extra flags)
     ("rt_abi.cu", []),
     ("rt_peak.cu", []),
 ]
-HEADERS = ["rt_kernel.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h")]
+HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h")]
 
 
 def _stale(target: str, deps: list) -> bool:
@@ -32,15 +32,18 @@ def _stale(target: str, deps: list) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, variant: str = "", defines: tuple = ()) -> str:
+    """variant/defines: dev-only A/B builds (csrc/librt_b200<variant>.so with extra -D flags,
+    loaded through the RT_B200_LIB environment variable); the product build takes neither."""
     hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
     objs, rebuilt = [], False
+    lib = LIB if not variant else LIB[:-3] + variant + ".so"
     for src, extra in UNITS:
         s = os.path.join(CSRC, src)
-        o = s[:-3] + ".o"
+        o = s[:-3] + variant + ".o"
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
-            cmd = [NVCC] + ARCH + COMMON + extra + ["-c", s, "-o", o]
+            cmd = [NVCC] + ARCH + COMMON + extra + [f"-D{d}" for d in defines] + ["-c", s, "-o", o]
             r = subprocess.run(cmd, capture_output=True, text=True)
             with open(o + ".log", "w") as f:
                 f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
@@ -49,11 +52,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
             if r.returncode != 0:
                 raise RuntimeError(f"nvcc failed on {src}")
             rebuilt = True
-    if force or rebuilt or _stale(LIB, objs):
-        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs
+    if force or rebuilt or _stale(lib, objs):
+        cmd = [NVCC] + ARCH + ["-shared", "-o", lib] + objs
         subprocess.run(cmd, check=True)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="-f" in sys.argv, verbose="-v" in sys.argv))
+    args = [a for a in sys.argv[1:] if not a.startswith("-")]
+    print(build(force="-f" in sys.argv, verbose="-v" in sys.argv, variant=args[0] if args else "",
+                defines=tuple(args[1:])))

@@ -3,6 +3,7 @@
 // replaces are cited in the header. No CPU rendering path exists here.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -27,6 +28,8 @@ struct rt_context {
   cudaEvent_t stage_done = nullptr; bool stage_pending = false;
   int n_obj = 0, n_planes = 0, n_lights = 0;
   size_t off_plane = 0, off_material = 0, off_lights = 0;   // in float4 units
+  // packet-kernel blob (appended to the same device buffer)
+  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0;
   // textures
   uint2* d_sky = nullptr; cudaArray_t sky_array = nullptr; cudaTextureObject_t sky_tex = 0; int sky_size = 0;
   unsigned char* d_noise = nullptr; int noise_w = 0, noise_h = 0;
@@ -35,6 +38,10 @@ struct rt_context {
   unsigned long long* d_counters = nullptr;
   uint64_t launches = 0;
   // e2e path
+  int host_path = RT_HOST_PATH_AUTO;
+  int coherent_override = -1;   // dev A/B: RT_PK_COHERENT=0/1
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t band_done[16] = {};
   cudaStream_t stream = nullptr;
   float4* o_color = nullptr; float4* o_position = nullptr; void* o_normal = nullptr; int* o_id = nullptr;
   size_t o_pixels = 0;
@@ -105,6 +112,65 @@ void stage_scene(const rt_object* obj, int n, const rt_light* lights, int m, int
   if (m > 0) std::memcpy(lt, lights, (size_t)m * sizeof(rt_light));
 }
 
+// Object[]/Light[] -> the packet kernel's shared-memory image (layout in rt_packet.cuh).
+// Returns the size in float4 units, or 0 when the scene cannot use the sign-select loops
+// (a non-finite bound). `out` may be null to size only.
+struct PkLayout { size_t float4s; int spheres, planes, lights_offset; };
+PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights, int m, float4* out) {
+  PkLayout L = {0, 0, 0, 0};
+  for (int i = 0; i < n; ++i) {
+    if (obj[i].type == 0) L.spheres++; else if (obj[i].type == 1) L.planes++;
+    if (obj[i].type == 0 || obj[i].type == 1)
+      for (int k = 0; k < 3; ++k)
+        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0};
+  }
+  size_t bytes = (size_t)L.spheres * 64 + (size_t)L.planes * 128 + (size_t)L.spheres * 4;
+  bytes = (bytes + 15) / 16 * 16;
+  L.lights_offset = (int)bytes;
+  bytes += (size_t)m * sizeof(rt_light);
+  L.float4s = bytes / 16;
+  if (L.float4s == 0) L.float4s = 1;
+  if (!out) return L;
+  std::memset(out, 0, L.float4s * 16);
+  char* base = (char*)out;
+  float* sph = (float*)base;
+  float* pln = (float*)(base + (size_t)L.spheres * 64);
+  int* sph_index = (int*)(base + (size_t)L.spheres * 64 + (size_t)L.planes * 128);
+  int ks = 0, kp = 0;
+  auto box = [](float* r, const rt_aabb& b) {          // per axis (lo,hi,hi,lo), lo <= hi
+    for (int k = 0; k < 3; ++k) {
+      const float lo = b.max[k] < b.min[k] ? b.max[k] : b.min[k];
+      const float hi = b.max[k] < b.min[k] ? b.min[k] : b.max[k];
+      r[4 * k + 0] = lo; r[4 * k + 1] = hi; r[4 * k + 2] = hi; r[4 * k + 3] = lo;
+    }
+  };
+  for (int i = 0; i < n; ++i) {
+    const rt_object& o = obj[i];
+    if (o.type == 0) {
+      float* r = sph + (size_t)ks * 16;
+      box(r, o.bounds);
+      r[12] = o.position[0]; r[13] = o.position[1]; r[14] = o.position[2]; r[15] = o.radius * o.radius;
+      sph_index[ks++] = i;
+    } else if (o.type == 1) {
+      float* r = pln + (size_t)kp * 32;
+      box(r, o.bounds);
+      const h3 nrm = {o.normal[0], o.normal[1], o.normal[2]};
+      h3 right, forward;                               // frame of glsl:130-138, hoisted per object
+      if (std::fabs(nrm.y) > 0.9f) right = hnormalize(hcross(nrm, h3{0.f, 0.f, 1.f}));
+      else right = hnormalize(hcross(nrm, h3{0.f, 1.f, 0.f}));
+      forward = hnormalize(hcross(right, nrm));
+      r[12] = nrm.x; r[13] = nrm.y; r[14] = nrm.z; r[15] = o.size[0] / 2.0f;
+      r[16] = right.x; r[17] = right.y; r[18] = right.z; r[19] = o.size[1] / 2.0f;
+      r[20] = forward.x; r[21] = forward.y; r[22] = forward.z; r[23] = 0.f;
+      r[24] = o.position[0]; r[25] = o.position[1]; r[26] = o.position[2];
+      std::memcpy(&r[27], &i, 4);
+      kp++;
+    }
+  }
+  if (m > 0) std::memcpy(base + L.lights_offset, lights, (size_t)m * sizeof(rt_light));
+  return L;
+}
+
 rt_status ensure_outputs(rt_context* c, size_t pixels) {
   if (pixels <= c->o_pixels) return RT_OK;
   cudaFree(c->o_color); cudaFree(c->o_position); cudaFree(c->o_normal); cudaFree(c->o_id);
@@ -155,11 +221,19 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if ((e = cudaMalloc(&c->d_counters, sizeof(unsigned long long) * RT_CNT_COUNT)) != cudaSuccess) return bail(e);
   if ((e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * RT_CNT_COUNT)) != cudaSuccess) return bail(e);
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e);
+  if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e);
+  for (int i = 0; i < 16; ++i)
+    if ((e = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e);
   if ((e = cudaEventCreateWithFlags(&c->stage_done, cudaEventDisableTiming)) != cudaSuccess) return bail(e);
   float h2[64], h3t[64];
   for (int i = 0; i < 64; ++i) { h2[i] = halton_host(i, 2); h3t[i] = halton_host(i, 3); }
-  if ((e = rt::upload_tables_fast(h2, h3t)) != cudaSuccess) return bail(e);
-  if ((e = rt::upload_tables_parity(h2, h3t)) != cudaSuccess) return bail(e);
+  int order[16];                                       // PCSS probes sorted by offset (rt_packet.cuh)
+  for (int i = 0; i < 16; ++i) order[i] = i;
+  for (int i = 1; i < 16; ++i)
+    for (int j = i; j > 0 && h3t[order[j]] < h3t[order[j - 1]]; --j) { int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t; }
+  if ((e = rt::upload_tables_fast(h2, h3t, order)) != cudaSuccess) return bail(e);
+  if ((e = rt::upload_tables_parity(h2, h3t, order)) != cudaSuccess) return bail(e);
+  if (const char* e2 = getenv("RT_PK_COHERENT")) c->coherent_override = atoi(e2) ? 1 : 0;
   *out = c;
   return RT_OK;
 }
@@ -176,6 +250,8 @@ void rt_destroy(rt_context* c) {
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->stage_done) cudaEventDestroy(c->stage_done);
   if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  for (int i = 0; i < 16; ++i) if (c->band_done[i]) cudaEventDestroy(c->band_done[i]);
   delete c;
 }
 
@@ -189,7 +265,9 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
   int planes = 0;
   for (int i = 0; i < n; ++i) planes += (obj[i].type == 1);
   const size_t off_plane = (size_t)3 * n, off_material = off_plane + (size_t)3 * planes;
-  const size_t off_lights = off_material + (size_t)4 * n, total = off_lights + (size_t)6 * m;
+  const size_t off_lights = off_material + (size_t)4 * n, off_pk = off_lights + (size_t)6 * m;
+  const PkLayout pkl = stage_scene_packet(obj, n, (const rt_light*)lights, m, nullptr);
+  const size_t total = off_pk + pkl.float4s;
   const size_t need = (total > 0 ? total : 1) * sizeof(float4);
   if (c->stage_pending) { RT_CUDA(c, cudaEventSynchronize(c->stage_done)); c->stage_pending = false; }
   if (need > c->h_stage_cap) {
@@ -205,9 +283,12 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
     c->d_scene_cap = need * 2;
   }
   stage_scene(obj, n, (const rt_light*)lights, m, planes, c->h_stage, off_plane, off_material, off_lights);
+  if (pkl.float4s) stage_scene_packet(obj, n, (const rt_light*)lights, m, c->h_stage + off_pk);
   RT_CUDA(c, cudaMemcpyAsync(c->d_scene, c->h_stage, total * sizeof(float4), cudaMemcpyHostToDevice, stream));
   c->n_obj = n; c->n_planes = planes; c->n_lights = m;
   c->off_plane = off_plane; c->off_material = off_material; c->off_lights = off_lights;
+  c->off_pk = off_pk; c->pk_float4s = pkl.float4s; c->pk_spheres = pkl.spheres; c->pk_planes = pkl.planes;
+  c->pk_lights_offset = pkl.lights_offset;
   if (async) {
     RT_CUDA(c, cudaEventRecord(c->stage_done, stream));
     c->stage_pending = true;
@@ -306,12 +387,28 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   kp.tile_counter = c->d_tile_counter; kp.tile_base = c->tile_base;
   kp.tiles_x = (unsigned)((p->width + 7) / 8);
   kp.tiles_y = (unsigned)((p->row_end - p->row_begin + 3) / 4);
+  kp.blocks_x = (kp.tiles_x + 3) / 4; kp.blocks_y = (kp.tiles_y + 1) / 2;
   kp.counters = c->d_counters;
+  // Kernel selection: the packet kernel (rt_packet.cuh) unless the caller asks for the literal
+  // one (counters need its reference-literal loops), renders a prefix of the uploaded arrays
+  // (the packet blob is staged for the full scene), or the scene does not fit shared memory.
+  const bool full_scene = p->num_objects == c->n_obj && p->num_lights == c->n_lights;
+  const bool use_packet = !(p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) && full_scene && c->pk_float4s > 0 &&
+                          c->pk_float4s * sizeof(float4) <= (size_t)c->max_smem_optin - 1024;
+  sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
+  sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
+  // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);
+  // with long loops the barrier imbalance costs more than the fetch locality gains.
+  sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : (c->pk_spheres + c->pk_planes <= 48 ? 1 : 0);
   unsigned warps = 0;
-  cudaError_t e = (p->flags & RT_FLAG_PARITY_MATH) ? rt::launch_render_parity(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps)
-                                                   : rt::launch_render_fast(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps);
+  const bool par = (p->flags & RT_FLAG_PARITY_MATH) != 0u;
+  cudaError_t e;
+  if (use_packet) e = par ? rt::launch_packet_parity(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps)
+                          : rt::launch_packet_fast(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps);
+  else e = par ? rt::launch_render_parity(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps)
+               : rt::launch_render_fast(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps);
   if (e != cudaSuccess) return cuda_fail(c, e, "rt_render launch");
-  c->tile_base += kp.tiles_x * kp.tiles_y + warps;     // every warp over-fetches exactly once
+  c->tile_base += kp.tiles_x * kp.tiles_y + warps;   // unsigned wrap-around is intended     // tiles + the over-fetch the launcher reports (one per warp / CTA round)
   c->launches += 1;
   return RT_OK;
 }
@@ -326,19 +423,70 @@ rt_status rt_render_host(rt_context* c, const rt_frame_params* p, const void* ob
     st = rt_upload_scene(c, objects, n, lights, m, c->stream, 1);
     if (st != RT_OK) return st;
   }
+  // How the three images reach the host (rt_set_host_path):
+  //   ZEROCOPY  pinned host buffers are mapped into the device address space (UVA), so the
+  //             kernel's float4 stores go straight over PCIe while later tiles are still being
+  //             traced: no device-side frame, no separate copy.
+  //   BANDED    rows are rendered in bands; band k is copied D2H on a second stream while band
+  //             k+1 renders.
+  //   STAGED    render the frame, then copy it (the v0 behaviour).
+  int path = c->host_path;
+  auto mapped = [](const void* h) -> bool {
+    if (!h) return true;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost && a.devicePointer == h;
+  };
+  const bool all_mapped = mapped(h_color) && mapped(h_position) && mapped(h_normal) && mapped(h_object_id);
+  if (path == RT_HOST_PATH_AUTO) path = all_mapped ? RT_HOST_PATH_BANDED : RT_HOST_PATH_STAGED;
+  if (path == RT_HOST_PATH_ZEROCOPY && !all_mapped) path = RT_HOST_PATH_STAGED;
+  if (path == RT_HOST_PATH_ZEROCOPY) {
+    st = rt_render(c, p, h_color, h_position, h_normal, h_object_id, c->stream);
+    if (st != RT_OK) return st;
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+  }
   const size_t pixels = (size_t)p->width * p->height;
   st = ensure_outputs(c, pixels);
   if (st != RT_OK) return st;
-  st = rt_render(c, p, h_color ? (float*)c->o_color : nullptr, h_position ? (float*)c->o_position : nullptr,
-                 h_normal ? c->o_normal : nullptr, h_object_id ? c->o_id : nullptr, c->stream);
-  if (st != RT_OK) return st;
-  const size_t first = (size_t)p->row_begin * p->width, count = (size_t)(p->row_end - p->row_begin) * p->width;
   const size_t nbytes = (p->flags & RT_FLAG_NORMAL_FP32) ? sizeof(float4) : sizeof(uint2);
-  if (h_color) RT_CUDA(c, cudaMemcpyAsync(h_color + first * 4, c->o_color + first, count * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-  if (h_position) RT_CUDA(c, cudaMemcpyAsync(h_position + first * 4, c->o_position + first, count * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-  if (h_normal) RT_CUDA(c, cudaMemcpyAsync((char*)h_normal + first * nbytes, (char*)c->o_normal + first * nbytes, count * nbytes, cudaMemcpyDeviceToHost, c->stream));
-  if (h_object_id) RT_CUDA(c, cudaMemcpyAsync(h_object_id + first, c->o_id + first, count * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  const int rows = p->row_end - p->row_begin;
+  int bands = 1;
+  if (path == RT_HOST_PATH_BANDED) {                     // ~2 MB+ of output per band, at most 16 bands
+    const size_t row_bytes = (size_t)p->width * 40;
+    bands = (int)(((size_t)rows * row_bytes) / (6u << 20));
+    if (bands < 1) bands = 1;
+    if (bands > 16) bands = 16;
+  }
+  int per = ((rows + bands - 1) / bands + 3) / 4 * 4;    // band height: a multiple of the tile height
+  if (per < 4) per = 4;
+  int b = 0;
+  for (int r0 = p->row_begin; r0 < p->row_end; r0 += per, ++b) {
+    rt_frame_params q = *p;
+    q.row_begin = r0;
+    q.row_end = r0 + per < p->row_end ? r0 + per : p->row_end;
+    st = rt_render(c, &q, h_color ? (float*)c->o_color : nullptr, h_position ? (float*)c->o_position : nullptr,
+                   h_normal ? c->o_normal : nullptr, h_object_id ? c->o_id : nullptr, c->stream);
+    if (st != RT_OK) return st;
+    cudaStream_t cs = bands > 1 ? c->copy_stream : c->stream;
+    if (bands > 1) {
+      RT_CUDA(c, cudaEventRecord(c->band_done[b & 15], c->stream));
+      RT_CUDA(c, cudaStreamWaitEvent(cs, c->band_done[b & 15], 0));
+    }
+    const size_t first = (size_t)q.row_begin * p->width, count = (size_t)(q.row_end - q.row_begin) * p->width;
+    if (h_color) RT_CUDA(c, cudaMemcpyAsync(h_color + first * 4, c->o_color + first, count * sizeof(float4), cudaMemcpyDeviceToHost, cs));
+    if (h_position) RT_CUDA(c, cudaMemcpyAsync(h_position + first * 4, c->o_position + first, count * sizeof(float4), cudaMemcpyDeviceToHost, cs));
+    if (h_normal) RT_CUDA(c, cudaMemcpyAsync((char*)h_normal + first * nbytes, (char*)c->o_normal + first * nbytes, count * nbytes, cudaMemcpyDeviceToHost, cs));
+    if (h_object_id) RT_CUDA(c, cudaMemcpyAsync(h_object_id + first, c->o_id + first, count * sizeof(int), cudaMemcpyDeviceToHost, cs));
+  }
   RT_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (bands > 1) RT_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+  return RT_OK;
+}
+
+rt_status rt_set_host_path(rt_context* c, int path) {
+  if (!c || path < RT_HOST_PATH_AUTO || path > RT_HOST_PATH_ZEROCOPY) return RT_ERR_INVALID_ARG;
+  c->host_path = path;
   return RT_OK;
 }
 

@@ -36,6 +36,14 @@ struct DeviceScene {
   int sky_size;
   const unsigned char* noise;  // R8
   int noise_w, noise_h;
+  // packet-kernel scene blob (rt_packet.cuh): sphere records (64 B), plane records (128 B),
+  // sphere_index (4 B each), padding to 16 B, raw light records (96 B). Copied verbatim into
+  // shared memory by every CTA. pk_float4s == 0: the packet kernel cannot take this scene.
+  const float4* pk_blob;
+  int pk_float4s;
+  int pk_num_spheres, pk_num_planes;
+  int pk_lights_offset;      // bytes from the start of the blob
+  int pk_coherent;           // 1: CTA-coherent phases (small scenes), 0: independent warps
 };
 
 struct KernelParams {
@@ -50,6 +58,7 @@ struct KernelParams {
   unsigned* tile_counter;    // monotonically increasing work counter (never reset)
   unsigned tile_base;        // value of the counter when this launch started
   unsigned tiles_x, tiles_y;
+  unsigned blocks_x, blocks_y;   // 32x8-pixel CTA blocks of the coherent mode (4x2 tiles)
   unsigned long long* counters;   // RT_CNT_COUNT reference-literal op counters
 };
 
@@ -60,7 +69,11 @@ size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights);
 cudaError_t launch_render_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
 cudaError_t launch_render_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
 
-cudaError_t upload_tables_fast(const float* halton2, const float* halton3);     // 64 entries each
-cudaError_t upload_tables_parity(const float* halton2, const float* halton3);
+cudaError_t launch_packet_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
+cudaError_t launch_packet_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
+
+// halton2/halton3: 64 entries each; probe_order: the 16 PCSS probe indices sorted by offset
+cudaError_t upload_tables_fast(const float* halton2, const float* halton3, const int* probe_order);
+cudaError_t upload_tables_parity(const float* halton2, const float* halton3, const int* probe_order);
 
 }  // namespace rt

@@ -3,12 +3,18 @@
 #define RT_PARITY 0
 #define RT_VARIANT_NS fast
 #include "rt_kernel.cuh"
+#include "rt_packet.cuh"
 
 namespace rt {
 cudaError_t launch_render_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   return fast::launch_render(kp, sm_count, stream, warps_launched);
 }
-cudaError_t upload_tables_fast(const float* halton2, const float* halton3) {
-  return fast::upload_tables(halton2, halton3);
+cudaError_t launch_packet_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+  return fast::pk::launch_packet(kp, sm_count, stream, warps_launched);
+}
+cudaError_t upload_tables_fast(const float* halton2, const float* halton3, const int* probe_order) {
+  cudaError_t e = fast::upload_tables(halton2, halton3);
+  if (e != cudaSuccess) return e;
+  return fast::pk::upload_probe_order(probe_order);
 }
 }  // namespace rt

@@ -1,0 +1,658 @@
+// rt_packet.cuh — the product kernel of librt_b200.so: the reference's per-pixel ray-tracing
+// pass (/root/reference/shader/raytracingCs.glsl) restructured around what ncu showed bounds
+// it on B200 (profiles/r01_v0_*): the ALU pipe (FMNMX/FSETP issue at half rate), a 170 KB
+// instruction footprint, and 124 registers. Same results as the literal kernel
+// (rt_kernel.cuh) — bit-identical in the parity build, tests/test_parity_gpu.py — from:
+//
+//   * sign-select slabs: every box is staged per axis as (lo,hi,hi,lo); a lane reads the
+//     8-byte (near,far) pair its ray's sign picks, so min(t0,t1)/max(t0,t1) cost no
+//     instruction. (near-o)*inv is the same two IEEE operations as the shader's
+//     (boxMin-origin)*invDir, issued as packed FADD2/FMUL2 (f32x2). Rays with a zero,
+//     denormal, infinite or NaN direction component take a generic min/max loop instead.
+//   * shadow packets: the 4 PCF samples (and 4 of the 16 PCSS probes) of one shading point
+//     share their origin and almost always their direction signs, so one lane traces them
+//     as a 4-ray packet: box loads and (near-o) are shared, four independent dependency
+//     chains hide latency at 16 warps/SM.
+//   * exact work skipping: a light whose BRDF term is exactly (0,0,0) cannot change Lo
+//     whatever its (finite) shadow factor is, so its shadow rays are not traced; shadow and
+//     probe rays stop at the first occluder (any-hit), PCSS stops at the first blocked probe.
+//   * spheres and planes are staged in separate arrays (no type branch per object); ties in t
+//     are resolved to the lower original index, which is what the shader's in-order strict
+//     `<` does.
+//   * one copy of each trace loop in the instruction stream (PCSS probes and PCF samples go
+//     through the same packet site).
+#pragma once
+#include "rt_math.cuh"
+
+namespace rt {
+namespace RT_VARIANT_NS {
+namespace pk {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kTileW = 8, kTileH = 4;            // one warp = 8x4 pixels
+
+// PCSS probe indices sorted by their offset halton3(i)*2-1: consecutive probes lie next to
+// each other on the line lightDir + rv*(1,1,1)*2s, so a packet of 4 rarely straddles a sign
+// change. The order cannot change the result (only "is any probe blocked" is used, glsl:425).
+__constant__ int c_probe_order[16];
+
+// ---------------------------------------------------------------- packed f32x2 (FADD2 / FMUL2)
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  float2 r;
+  asm("{ .reg .b64 ra, rb, rc; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; add.rn.f32x2 rc, ra, rb; mov.b64 {%0, %1}, rc; }"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return r;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  float2 r;
+  asm("{ .reg .b64 ra, rb, rc; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; mul.rn.f32x2 rc, ra, rb; mov.b64 {%0, %1}, rc; }"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return r;
+}
+__device__ __forceinline__ float2 dup2(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }   // FMNMX3
+__device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf(fminf(a, b), c); }
+
+// 1/x for shadow-ray slabs: IEEE in the parity build, MUFU.RCP in the fast build (a shadow ray
+// only yields a boolean; 1 ulp of inv moves the slab boundary by 1 ulp).
+#if RT_PARITY
+__device__ __forceinline__ float rcp_shadow(float x) { return __frcp_rn(x); }
+__device__ __forceinline__ f3 normalize_shadow(f3 a) { return normalize_ieee(a); }
+#else
+__device__ __forceinline__ float rcp_shadow(float x) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ f3 normalize_shadow(f3 a) { return a * rsqrtf(dot3(a, a)); }
+#endif
+
+// ---------------------------------------------------------------- shared-memory scene
+// Byte layout, built on the host by stage_scene_packet() (rt_abi.cu):
+//   sphere record  64 B : x(lo,hi,hi,lo) y(lo,hi,hi,lo) z(lo,hi,hi,lo) (cx,cy,cz,r*r)
+//   plane record  128 B : the same 48-B box, (n.xyz, size.x/2) (right.xyz, size.y/2)
+//                         (forward.xyz, 0) (position.xyz, original index bits) + 16 B pad
+//   sphere_index   4 B  : original object index of each sphere slot
+// lo/hi are sorted per axis on the host (the shader's min/max make the test symmetric in them).
+constexpr int kSphereBytes = 64, kPlaneBytes = 128;
+
+typedef unsigned saddr;        // 32-bit shared-window address: explicit LDS, one register
+struct Scene {
+  saddr sph;                  // shared memory
+  saddr pln;                  // shared memory
+  saddr sph_index;            // shared memory
+  saddr lights;               // shared memory, raw 96-B records
+  const float4* material;     // global memory, 4 float4 per ORIGINAL object index
+  int ns, np, nl;
+  float maxd;
+};
+
+__device__ __forceinline__ float lds32(saddr p) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(p)); return v; }
+__device__ __forceinline__ int lds32i(saddr p) { int v; asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(p)); return v; }
+__device__ __forceinline__ float2 lds64(saddr p) {
+  float2 v; asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(p)); return v;
+}
+__device__ __forceinline__ float4 lds128(saddr p) {
+  float4 v; asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(p)); return v;
+}
+
+// Direction usable by the sign-select loops: every component normal, finite and non-zero
+// (then inv is finite and non-zero, so no 0*inf NaN can appear and min/max are decided by sign).
+__device__ __forceinline__ bool dir_regular(f3 d, float a) {
+  return fmin3(fabsf(d.x), fabsf(d.y), fabsf(d.z)) > 1.0e-30f && a < 1.0e30f;   // a = dot(d,d): NaN/inf fail
+}
+
+// intersectSphere (glsl:105-118), a = dot(d,d) hoisted; sp = (centre, r*r).
+__device__ __forceinline__ bool sphere_t(float4 sp, f3 o, f3 d, float a, float& t) {
+  const f3 oc = o - xyz(sp);
+  const float b = 2.0f * dot3(oc, d);
+  const float c = dot3(oc, oc) - sp.w;
+  const float disc = b * b - 4.0f * a * c;
+  if (disc < 0.0f) return false;
+  t = div_ieee(-b - sqrt_ieee(disc), 2.0f * a);
+  return t > 0.0f;
+}
+
+// "near root in (0, lim)" for shadow rays. Parity build: the literal root. Fast build: the
+// same predicate without sqrt/div — t>0 <=> b<0 && c>0 (a>0); t<lim <=> sqrt(disc) > -b-2a*lim.
+__device__ __forceinline__ bool sphere_any(f3 oc, float cc, f3 d, float a, float lim) {
+  const float b = 2.0f * dot3(oc, d);
+  const float disc = b * b - 4.0f * a * cc;
+#if RT_PARITY
+  if (disc < 0.0f) return false;
+  const float t = div_ieee(-b - sqrt_ieee(disc), 2.0f * a);
+  return t > 0.0f && t < lim;
+#else
+  const float q = -b - 2.0f * a * lim;
+  return disc >= 0.0f && b < 0.0f && cc > 0.0f && (q < 0.0f || disc > q * q);
+#endif
+}
+
+// intersectPlane (glsl:120-153) on a plane record; the frame is hoisted to staging time.
+__device__ __forceinline__ bool plane_t(saddr rec, f3 o, f3 d, float& t) {
+  const float4 pn = lds128(rec + 48), pp = lds128(rec + 96);
+  const f3 n = xyz(pn);
+  const float denom = dot3(n, d);
+  if (!(fabsf(denom) > 1e-6f)) return false;
+  t = div_ieee(dot3(xyz(pp) - o, n), denom);
+  if (t < 0.0f) return false;
+  const float4 pr = lds128(rec + 64), pf = lds128(rec + 80);
+  const f3 local = (o + d * t) - xyz(pp);
+  const float x = dot3(local, xyz(pr));
+  const float z = dot3(local, xyz(pf));
+  if (fabsf(x) > pn.w || fabsf(z) > pr.w) return false;
+  return true;
+}
+
+struct Hit { int code; float t; };     // code: sphere slot k, or ns + plane slot; -1 = miss
+
+__device__ __forceinline__ int hit_object_index(const Scene& s, int code) {
+  return code < s.ns ? lds32i(s.sph_index + 4u * (unsigned)code) : lds32i(s.pln + (unsigned)(code - s.ns) * kPlaneBytes + 108u);
+}
+
+// One ray against the whole scene. ANY: stop at the first hit with 0 < t < lim (shadow rays;
+// `hit && closestT < L` of glsl:388-392 <=> such a hit exists). Otherwise closest hit with the
+// shader's tie rule. GENERIC: explicit min/max per axis (any direction, incl. NaN and 0).
+template <bool ANY, bool GENERIC>
+__device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, float a, float lim) {
+  // per-axis running addresses of the (near,far) pair this ray's sign selects
+  saddr ax = s.sph + ((!GENERIC && d.x < 0.0f) ? 8u : 0u);
+  saddr ay = s.sph + ((!GENERIC && d.y < 0.0f) ? 24u : 16u);
+  saddr az = s.sph + ((!GENERIC && d.z < 0.0f) ? 40u : 32u);
+  const float nox = -o.x, noy = -o.y, noz = -o.z;
+  Hit h; h.code = -1; h.t = ANY ? lim : s.maxd;
+  auto slab = [&](unsigned off) -> bool {
+    const float2 X = mul2(add2(lds64(ax + off), dup2(nox)), dup2(inv.x));
+    const float2 Y = mul2(add2(lds64(ay + off), dup2(noy)), dup2(inv.y));
+    const float2 Z = mul2(add2(lds64(az + off), dup2(noz)), dup2(inv.z));
+    float tmin, tmax;
+    if (GENERIC) {
+      tmin = fmax3(fminf(X.x, X.y), fminf(Y.x, Y.y), fminf(Z.x, Z.y));
+      tmax = fmin3(fmaxf(X.x, X.y), fmaxf(Y.x, Y.y), fmaxf(Z.x, Z.y));
+    } else {
+      tmin = fmax3(X.x, Y.x, Z.x);
+      tmax = fmin3(X.y, Y.y, Z.y);
+    }
+    return tmax >= tmin && tmin < s.maxd && tmax > 0.0f;      // glsl:102
+  };
+  auto sphere = [&](int k) -> bool {                           // true: ANY hit found
+    float t;
+    if (sphere_t(lds128(s.sph + (unsigned)k * kSphereBytes + 48u), o, d, a, t) && t < h.t) {   // t > 0 checked in sphere_t
+      h.code = k;
+      if (ANY) return true;
+      h.t = t;
+    }
+    return false;
+  };
+  int k = 0;
+  for (; k + 2 <= s.ns; k += 2, ax += 2 * kSphereBytes, ay += 2 * kSphereBytes, az += 2 * kSphereBytes) {
+    const bool p0 = slab(0u), p1 = slab((unsigned)kSphereBytes);
+    if (p0 | p1) {
+      if (p0 && sphere(k)) return h;
+      if (p1 && sphere(k + 1)) return h;
+    }
+  }
+  if (k < s.ns && slab(0u) && sphere(k)) return h;
+  const unsigned tail = (unsigned)(s.ns - k) * kSphereBytes;   // s.pln follows the sphere records
+  ax += tail; ay += tail; az += tail;
+  saddr rec = s.pln;
+  for (int j = 0; j < s.np; ++j, rec += kPlaneBytes, ax += kPlaneBytes, ay += kPlaneBytes, az += kPlaneBytes) {
+    if (!slab(0u)) continue;
+    float t;
+    if (!plane_t(rec, o, d, t) || !(t > 0.0f)) continue;
+    if (ANY) {
+      if (t < h.t) { h.code = s.ns + j; return h; }
+    } else if (t < h.t || (t == h.t && h.code >= 0 && lds32i(rec + 108u) < hit_object_index(s, h.code))) {
+      h.t = t; h.code = s.ns + j;
+    }
+  }
+  if (ANY) h.code = -1;
+  return h;
+}
+
+// The cold variants live behind calls so the hot loops stay small in the instruction cache.
+__device__ __noinline__ Hit trace_closest_generic(const Scene& s, f3 o, f3 d, f3 inv, float a) {
+  return trace_one<false, true>(s, o, d, inv, a, 0.0f);
+}
+__device__ __noinline__ bool trace_any_one(const Scene& s, f3 o, f3 d, float lim) {
+  const float a = dot3(d, d);
+  const f3 inv = mk3(rcp_shadow(d.x), rcp_shadow(d.y), rcp_shadow(d.z));
+  if (dir_regular(d, a)) return trace_one<true, false>(s, o, d, inv, a, lim).code >= 0;
+  const f3 inv_ieee = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
+  return trace_one<true, true>(s, o, d, inv_ieee, a, lim).code >= 0;
+}
+
+// Closest hit for primary / bounce / SSS rays (glsl:155-196). IEEE 1/dir in both builds: the
+// hit set of these rays feeds P and N.
+__device__ __forceinline__ Hit trace_closest(const Scene& s, f3 o, f3 d) {
+  const f3 inv = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
+  const float a = dot3(d, d);
+  if (!dir_regular(d, a)) return trace_closest_generic(s, o, d, inv, a);
+  return trace_one<false, false>(s, o, d, inv, a, 0.0f);
+}
+
+// 4 shadow rays with a common origin. Returns the mask of rays that hit something with
+// 0 < t < lim. Rays outside `active` must carry a copy of an active ray's direction.
+__device__ __forceinline__ unsigned trace_any_packet(const Scene& s, f3 o, const f3 (&d)[4], unsigned active, float lim) {
+  float a[4];
+  float2 ivx[4], ivy[4], ivz[4];
+  bool regular = true;
+  unsigned sx = 0u, sy = 0u, sz = 0u;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    a[r] = dot3(d[r], d[r]);
+    regular = regular && dir_regular(d[r], a[r]);
+    sx |= __float_as_uint(d[r].x) ^ __float_as_uint(d[0].x);
+    sy |= __float_as_uint(d[r].y) ^ __float_as_uint(d[0].y);
+    sz |= __float_as_uint(d[r].z) ^ __float_as_uint(d[0].z);
+    ivx[r] = dup2(rcp_shadow(d[r].x)); ivy[r] = dup2(rcp_shadow(d[r].y)); ivz[r] = dup2(rcp_shadow(d[r].z));   // FMUL2 takes the scalar broadcast form
+  }
+  if (!regular || ((sx | sy | sz) >> 31)) {            // mixed signs or an irregular direction: ray by ray
+    unsigned occ = 0u;
+#pragma unroll 1
+    for (int r = 0; r < 4; ++r) {
+      if (!((active >> r) & 1u)) continue;
+      const f3 dr = r == 0 ? d[0] : (r == 1 ? d[1] : (r == 2 ? d[2] : d[3]));
+      if (trace_any_one(s, o, dr, lim)) occ |= 1u << r;
+    }
+    return occ;
+  }
+  saddr ax = s.sph + (d[0].x < 0.0f ? 8u : 0u), ay = s.sph + (d[0].y < 0.0f ? 24u : 16u), az = s.sph + (d[0].z < 0.0f ? 40u : 32u);
+  const float nox = -o.x, noy = -o.y, noz = -o.z;
+  unsigned occ = 0u;
+  bool pass[4];
+  auto slabs = [&]() -> bool {
+    const float2 X = add2(lds64(ax), dup2(nox)), Y = add2(lds64(ay), dup2(noy)), Z = add2(lds64(az), dup2(noz));
+    bool any = false;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const float2 tx = mul2(X, ivx[r]), ty = mul2(Y, ivy[r]), tz = mul2(Z, ivz[r]);
+      const float tmin = fmax3(tx.x, ty.x, tz.x), tmax = fmin3(tx.y, ty.y, tz.y);
+      pass[r] = tmax >= tmin && tmin < s.maxd && tmax > 0.0f;
+      any = any || pass[r];
+    }
+    return any;
+  };
+  saddr rec = s.sph;
+#pragma unroll 1
+  for (int k = 0; k < s.ns; ++k, rec += kSphereBytes, ax += kSphereBytes, ay += kSphereBytes, az += kSphereBytes) {
+    if (!slabs()) continue;
+    const float4 sp = lds128(rec + 48u);
+    const f3 oc = o - xyz(sp);
+    const float cc = dot3(oc, oc) - sp.w;
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+      if (pass[r] && !((occ >> r) & 1u) && sphere_any(oc, cc, d[r], a[r], lim)) occ |= 1u << r;
+    if ((occ & active) == active) return occ;
+  }
+#pragma unroll 1
+  for (int j = 0; j < s.np; ++j, rec += kPlaneBytes, ax += kPlaneBytes, ay += kPlaneBytes, az += kPlaneBytes) {
+    if (!slabs()) continue;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      float t;
+      if (pass[r] && !((occ >> r) & 1u) && plane_t(rec, o, d[r], t) && t > 0.0f && t < lim) occ |= 1u << r;
+    }
+    if ((occ & active) == active) return occ;
+  }
+  return occ;
+}
+
+// ---------------------------------------------------------------- shading
+struct LightRec {
+  int type; f3 position, direction, color; float intensity, shadowSoftness; int shadowType, pcfSamples; float lightSize;
+};
+__device__ __forceinline__ LightRec load_light(const Scene& s, int i) {
+  const saddr l = s.lights + (unsigned)i * 96u;          // rt_light offsets (include/rt_abi.h)
+  const float4 q1 = lds128(l + 16u), q2 = lds128(l + 32u), q3 = lds128(l + 48u);
+  LightRec r;
+  r.type = lds32i(l);
+  r.position = xyz(q1); r.direction = xyz(q2); r.color = xyz(q3); r.intensity = q3.w;
+  r.shadowSoftness = lds32(l + 72u); r.shadowType = lds32i(l + 76u);
+  r.pcfSamples = lds32i(l + 80u); r.lightSize = lds32(l + 84u);
+  return r;
+}
+__device__ __forceinline__ Mat load_material(const Scene& s, int index) {
+  const float4 m0 = __ldg(s.material + 4 * index + 0), m1 = __ldg(s.material + 4 * index + 1);
+  const float4 m2 = __ldg(s.material + 4 * index + 2), m3 = __ldg(s.material + 4 * index + 3);
+  Mat m;
+  m.albedo = xyz(m0); m.metallic = m0.w;
+  m.roughness = m1.x; m.diffuseStrength = m1.y; m.ior = m1.z; m.transparency = m1.w;
+  m.subsurfaceColor = xyz(m2); m.subsurfaceScatter = m2.w; m.scatterDistance = m3.x;
+  return m;
+}
+
+// calculateShadow (glsl:442-455) for shadowType 1 (pcfShadow, glsl:342-397) and 2 (pcssShadow,
+// glsl:400-440 = "fully lit unless one of 16 fixed probes is blocked, else PCF"). Probes and PCF
+// samples run through ONE packet site: jobs [0,nprobe) are probes, [nprobe,nprobe+pcf) samples.
+__device__ __forceinline__ float shadow_packets(const Scene& s, float noise_r, f3 origin, const LightRec& light,
+                                                f3 lightDir, float lightDistance) {
+  const int nprobe = light.shadowType == 2 ? 16 : 0;
+  const int total = nprobe + (light.pcfSamples > 0 ? light.pcfSamples : 0);
+  const f3 tangent = normalize_ieee(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
+  const f3 bitangent = cross3(lightDir, tangent);
+  const float filterSize = light.shadowSoftness * 0.005f;                        // glsl:364 (overwrites :352)
+  const float searchSize = light.lightSize * 0.1f;                               // glsl:404
+  // t < lightDistance && t < maxRayDistance as one bound; a NaN distance stays NaN (never occluded)
+  const float lim_light = lightDistance > s.maxd ? s.maxd : lightDistance;
+  const float lim_pcf = (light.type == 0 || light.type == 2) ? lim_light : s.maxd;   // glsl:388-392
+  const float lim_probe = light.type != 1 ? lim_light : s.maxd;                      // glsl:419-423
+  int unoccluded = 0;
+  int j = 0;
+  while (j < total) {
+    const bool probing = j < nprobe;
+    const int end = probing ? nprobe : total;
+    f3 d[4];
+    unsigned active = 0u;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int idx = j + r;
+      if (idx < end) {
+        active |= 1u << r;
+        if (probing) {
+          const float rv = halton3(c_probe_order[idx]) * 2.0f - 1.0f;                       // glsl:408
+          d[r] = normalize_shadow((lightDir + rv * searchSize) + rv * searchSize);           // glsl:409
+        } else {
+          const int i = idx - nprobe;
+          const float rx = fract_(halton2(i) + noise_r);                                     // glsl:366-367
+          const float ry = fract_(halton3(i) + 0.0f);
+          f3 v = (lightDir + (rx * tangent) * filterSize) + (ry * bitangent) * filterSize;   // glsl:371-378
+          if (light.type != 1) v = normalize_shadow(v);
+          d[r] = v;
+        }
+      } else {
+        d[r] = d[0];
+      }
+    }
+    const unsigned occ = trace_any_packet(s, origin, d, active, probing ? lim_probe : lim_pcf) & active;
+    if (probing) {
+      if (occ) { j = nprobe; continue; }                 // a blocker exists: go to the PCF phase
+      j += 4;
+      if (j >= nprobe) return 1.0f;                      // glsl:428-430: no blocker -> fully lit
+    } else {
+      unoccluded += __popc(active & ~occ);
+      j += 4;
+    }
+  }
+  return div_ieee((float)unoccluded, (float)light.pcfSamples);     // 0/0 = NaN when pcfSamples == 0
+}
+
+// computeSubsurfaceScattering (glsl:316-339); unreachable from the reference's UI and scene files.
+__device__ __noinline__ f3 subsurface(const Scene& s, f3 P, f3 N, const Mat& mat) {
+  f3 sss = mk3(0.0f, 0.0f, 0.0f);
+  for (int i = 0; i < 4; ++i) {
+    const f3 d = cosine_hemisphere((float)i / 4.0f, halton(i, 2), N);
+    const f3 o = P + N * 0.001f;
+    const f3 inv = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
+    const Hit h = trace_closest_generic(s, o, d, inv, dot3(d, d));
+    if (h.code >= 0) {
+      const float attenuation = expf(div_shade(-h.t, mat.scatterDistance));
+      sss = sss + xyz(__ldg(s.material + 4 * hit_object_index(s, h.code))) * attenuation;
+    }
+  }
+  const f3 v = (sss * mat.subsurfaceColor) * mat.subsurfaceScatter;
+  return mk3(v.x / 4.0f, v.y / 4.0f, v.z / 4.0f);
+}
+
+// Phase barrier of the CTA-coherent mode (see the kernel): keeps the warps that share an SM
+// sub-partition inside the same stretch of code. `coh` is kernel-uniform.
+__device__ __forceinline__ void phase_sync(bool coh) { if (coh) __syncthreads(); }
+
+// computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
+// lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
+// Every lane of the CTA walks the light loop (lit = this lane has a surface to shade).
+__device__ __forceinline__ f3 compute_lighting(const Scene& s, bool coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
+  f3 Lo = mk3(0.0f, 0.0f, 0.0f);
+  const f3 shadow_origin = P + N * 0.001f;               // glsl:381, :412
+#pragma unroll 1
+  for (int i = 0; i < s.nl; ++i) {
+    phase_sync(coh);
+    if (!lit) continue;
+    const LightRec light = load_light(s, i);
+    f3 lightDir = mk3(0.0f, 0.0f, 0.0f);
+    float attenuation = 1.0f, lightDistance = 0.0f;
+    if (light.type == 0) {
+      lightDir = light.position - P;
+      lightDistance = sqrt_ieee(dot3(lightDir, lightDir));
+      attenuation = div_shade(1.0f, 1.0f + 0.1f * lightDistance + 0.01f * lightDistance * lightDistance);
+      lightDir = normalize_ieee(lightDir);
+    } else if (light.type == 1) {
+      lightDir = normalize_ieee(-light.direction);
+      lightDistance = 1e6f;
+    } else if (light.type == 2) {
+      lightDir = light.position - P;
+      lightDistance = sqrt_ieee(dot3(lightDir, lightDir));
+      lightDir = normalize_ieee(lightDir);
+      attenuation = div_shade(1.0f, lightDistance * lightDistance);
+      const f3 lightNormal = normalize_shade(light.direction);
+      attenuation *= fmaxf(dot3(lightDir, lightNormal), 0.0f);   // P->light vs facing
+    }
+    const f3 L = normalize_shade(lightDir);
+    const f3 H = normalize_shade(V + L);
+    const f3 radiance = (light.color * attenuation) * light.intensity;
+    const f3 brdf = compute_pbr(mat, N, V, L, H, radiance);
+    const bool sampled = light.shadowType == 1 || light.shadowType == 2;
+    // exactly zero (not NaN) and the shadow factor is finite (pcfSamples == 0 gives 0/0)
+    if (brdf.x == 0.0f && brdf.y == 0.0f && brdf.z == 0.0f && (!sampled || light.pcfSamples > 0)) continue;
+    float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
+    if (light.shadowType == 0) shadowFactor = 1.0f;
+    else if (sampled) shadowFactor = shadow_packets(s, noise_r, shadow_origin, light, lightDir, lightDistance);
+    Lo = Lo + brdf * shadowFactor;
+  }
+  if (lit && mat.subsurfaceScatter > 0.0f) Lo = Lo + subsurface(s, P, N, mat);
+  return Lo;
+}
+
+// ---------------------------------------------------------------- main (glsl:509-584)
+struct PixelResult { f3 color, P, N; int object_id; };
+
+// One invocation of the shader's main() per lane. Whole warps (coh: the whole CTA) call this
+// together; `alive` = this lane still has a path to extend (false from the start for lanes
+// outside the image). The bounce loop ends when no lane of the warp / CTA is alive.
+__device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, bool coh,
+                                                   bool alive, unsigned px, unsigned py, int frame_count) {
+  const rt_frame_params& fp = kp.fp;
+  const float noise_r = fetch_noise(tx, (float)(px + (unsigned)frame_count) * fp.noise_scale[0],
+                                    (float)(py + (unsigned)frame_count) * fp.noise_scale[1]);
+  // generateCameraRay (glsl:198-217); jitter = texel.xy*2-1 with .y = 0 for an R8 texture.
+  const float jx = noise_r * 2.0f - 1.0f, jy = 0.0f * 2.0f - 1.0f;
+  float ux = div_ieee((float)(int)px + 0.5f + jx, (float)fp.width);
+  float uy = div_ieee((float)(int)py + 0.5f + jy, (float)fp.height);
+  ux = ux * 2.0f - 1.0f;
+  uy = uy * 2.0f - 1.0f;
+  ux *= kp.aspect * kp.tan_fov * fp.focal_length;
+  uy *= kp.tan_fov * fp.focal_length;
+  const f3 camDir = mk3(fp.camera_dir[0], fp.camera_dir[1], fp.camera_dir[2]);
+  const f3 camRight = mk3(fp.camera_right[0], fp.camera_right[1], fp.camera_right[2]);
+  const f3 camUp = mk3(fp.camera_up[0], fp.camera_up[1], fp.camera_up[2]);
+  f3 ro = mk3(fp.camera_pos[0], fp.camera_pos[1], fp.camera_pos[2]);
+  f3 rd = normalize_ieee((camDir + ux * camRight) + uy * camUp);
+
+  PixelResult out;
+  out.color = mk3(0.0f, 0.0f, 0.0f);
+  out.P = mk3(0.0f, 0.0f, 0.0f);               // P = N = 0 on a primary miss
+  out.N = mk3(0.0f, 0.0f, 0.0f);
+  out.object_id = -1;
+  f3 throughput = mk3(1.0f, 1.0f, 1.0f);
+
+#pragma unroll 1
+  for (int depth = 0; depth < fp.max_ray_depth; ++depth) {
+    if (!(coh ? __syncthreads_or(alive) : __any_sync(0xffffffffu, alive))) break;
+    bool lit = false;
+    f3 N = mk3(0.0f, 0.0f, 0.0f), P = N, V = N;
+    Mat mat = {};
+    if (alive) {
+      const Hit h = trace_closest(s, ro, rd);
+      if (h.code < 0) {                         // miss path (glsl:530-534)
+        const f3 sky = fp.use_skybox ? fetch_sky(tx, rd) : mk3(0.0f, 0.0f, 0.0f);
+        out.color = out.color + throughput * sky;
+        alive = false;
+      } else {
+        lit = true;
+        const int index = hit_object_index(s, h.code);
+        if (h.code < s.ns) N = normalize_ieee((ro + rd * h.t) - xyz(lds128(s.sph + (unsigned)h.code * kSphereBytes + 48u)));   // glsl:186-191
+        else N = xyz(lds128(s.pln + (unsigned)(h.code - s.ns) * kPlaneBytes + 48u));
+        mat = load_material(s, index);
+        P = ro + rd * h.t;
+        V = normalize_shade(-rd);
+        out.P = P; out.N = N; out.object_id = index;
+      }
+    }
+    const f3 Lo = compute_lighting(s, coh, lit, noise_r, P, N, mat, V);
+    if (!lit) continue;
+    out.color = out.color + throughput * Lo;
+
+    if (depth > 2) {                            // Russian roulette (glsl:544-549)
+      const float diffuseWeight = sqrt_ieee(dot3(mat.albedo, mat.albedo)) * mat.diffuseStrength;
+      const float continueProb =
+          fminf(fmaxf(throughput.x, fmaxf(throughput.y, throughput.z)) * 0.95f + diffuseWeight, 0.99f);
+      if (random2((float)(px + (unsigned)depth), (float)(py + (unsigned)depth)) > continueProb) { alive = false; continue; }
+      throughput = mk3(div_ieee(throughput.x, continueProb), div_ieee(throughput.y, continueProb),
+                       div_ieee(throughput.z, continueProb));
+    }
+    if (depth + 1 >= fp.max_ray_depth) { alive = false; continue; }   // the next ray would never be traced
+
+    const float F = fresnel_schlick(fmaxf(dot3(V, N), 0.0f), mat.ior);
+    if (mat.diffuseStrength > 0.0f) {           // glsl:555-567
+      const int hi = depth * 64 + frame_count;
+      const f3 specularDir = reflect3(rd, N);
+      const f3 diffuseDir = cosine_hemisphere(div_ieee((float)hi, 64.0f), halton(hi, 2), N);
+      rd = normalize_ieee(mix3(specularDir, diffuseDir, mat.roughness));
+      ro = P + N * 0.001f;
+      throughput = throughput * (mat.albedo * mat.diffuseStrength);
+    } else if (mat.transparency > 0.0f) {       // glsl:568-571
+      rd = refraction_dir(rd, N, mat.ior);
+      ro = P - N * 0.001f;
+      throughput = throughput * ((mat.albedo * (1.0f - F)) * mat.transparency);
+    } else {                                    // glsl:572-576
+      rd = reflect3(rd, N);
+      ro = P + N * 0.001f;
+      throughput = throughput * (mat.albedo * F);
+    }
+  }
+  return out;
+}
+
+// ---------------------------------------------------------------- kernel
+#ifndef RT_PK_MINBLOCKS
+#define RT_PK_MINBLOCKS 2
+#endif
+__global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
+  extern __shared__ float4 smem[];
+  const DeviceScene& sc = kp.sc;
+  const rt_frame_params& fp = kp.fp;
+
+  // ---- stage the scene once per CTA: one contiguous copy of the host-built blob
+  for (int i = threadIdx.x; i < sc.pk_float4s; i += kThreads) smem[i] = __ldg(sc.pk_blob + i);
+  __syncthreads();
+  Scene s;
+  const saddr base = (saddr)__cvta_generic_to_shared(smem);
+  s.sph = base;
+  s.pln = base + (unsigned)sc.pk_num_spheres * kSphereBytes;
+  s.sph_index = s.pln + (unsigned)sc.pk_num_planes * kPlaneBytes;
+  s.lights = base + (unsigned)sc.pk_lights_offset;
+  s.material = sc.material;
+  s.ns = sc.pk_num_spheres; s.np = sc.pk_num_planes; s.nl = sc.num_lights;
+  s.maxd = fp.max_ray_distance;
+
+  Textures tx;
+  tx.sky = sc.sky; tx.sky_tex = sc.sky_tex; tx.sky_size = sc.sky_size;
+  tx.sky_hw = (fp.flags & RT_FLAG_SKYBOX_HW) != 0u && sc.sky_tex != 0ull;
+  tx.noise = sc.noise; tx.noise_w = sc.noise_w; tx.noise_h = sc.noise_h;
+
+  const int lane = threadIdx.x & 31;
+  const int lx = lane & (kTileW - 1), ly = lane >> 3;
+  const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
+  const int nsamp = fp.num_samples > 0 ? fp.num_samples : 1;
+  const float inv_ns = rcp_ieee((float)nsamp);
+
+  // Two work distributions over the same 8x4-pixel warp tiles (kp.sc.pk_coherent, host-chosen):
+  //  * coherent (small scenes): the CTA takes 8 tiles forming a 32x8-pixel block and walks the
+  //    shader in phases separated by CTA barriers, so that the warps sharing an SM sub-partition
+  //    fetch the same instructions at about the same time. Measured on B200 (C2): the
+  //    independent-warp loop is instruction-fetch bound (ncu: 62 % of warp samples stalled on
+  //    no_instruction), tile-level coherence alone gave +52 % throughput.
+  //  * independent (large scenes): every warp pulls its own tiles from the global counter; the
+  //    object loops are long, cheap sky tiles and expensive reflective tiles balance dynamically.
+  const bool coh = sc.pk_coherent != 0;
+  __shared__ unsigned s_tile;
+  unsigned tile = 0, next = 0;
+  if (!coh) {
+    if (lane == 0) tile = atomicAdd(kp.tile_counter, 1u) - kp.tile_base;
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+  }
+  for (;;) {
+    if (coh) {
+      __syncthreads();
+      if (threadIdx.x == 0) s_tile = atomicAdd(kp.tile_counter, 1u) - kp.tile_base;
+      __syncthreads();
+      const unsigned blk = s_tile;                       // block id: 4x2 tiles = 32x8 pixels
+      if (blk >= kp.blocks_x * kp.blocks_y) break;
+      const unsigned by = blk / kp.blocks_x, bx = blk - by * kp.blocks_x;
+      const unsigned w = threadIdx.x >> 5;
+      const unsigned tyi = by * 2u + (w >> 2), txi = bx * 4u + (w & 3u);
+      tile = (tyi < kp.tiles_y && txi < kp.tiles_x) ? tyi * kp.tiles_x + txi : num_tiles;
+    } else {
+      if (tile >= num_tiles) break;
+      if (lane == 0) next = atomicAdd(kp.tile_counter, 1u) - kp.tile_base;   // prefetch the next tile id
+    }
+    const unsigned ty = tile / kp.tiles_x, txi = tile - ty * kp.tiles_x;
+    const int px = (int)txi * kTileW + lx;
+    const int py = fp.row_begin + (int)ty * kTileH + ly;
+    const bool inside = tile < num_tiles && px < fp.width && py < fp.row_end;
+    PixelResult r;                                       // position/normal/id: those of sample 0
+#pragma unroll 1
+    for (int sidx = 0; sidx < nsamp; ++sidx) {           // colour: sequential FP32 sum over samples
+      const PixelResult r2 = shade_pixel(kp, s, tx, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
+      if (sidx == 0) r = r2;
+      else r.color = r.color + r2.color;
+    }
+    if (inside) {
+      const size_t at = (size_t)py * fp.width + px;
+      if (kp.color) {
+        float4 c = make_float4(r.color.x, r.color.y, r.color.z, 1.0f);
+        if (fp.flags & RT_FLAG_ACCUMULATE) {             // partial sums for sample-range sharding
+          const float4 old = kp.color[at];
+          c = make_float4(old.x + c.x, old.y + c.y, old.z + c.z, 1.0f);
+        } else if (nsamp > 1) {
+          c = make_float4(c.x * inv_ns, c.y * inv_ns, c.z * inv_ns, 1.0f);
+        }
+        kp.color[at] = c;
+      }
+      if (kp.position) kp.position[at] = make_float4(r.P.x, r.P.y, r.P.z, 1.0f);
+      if (kp.normal) {
+        if (fp.flags & RT_FLAG_NORMAL_FP32) reinterpret_cast<float4*>(kp.normal)[at] = make_float4(r.N.x, r.N.y, r.N.z, 1.0f);
+        else reinterpret_cast<uint2*>(kp.normal)[at] = pack_half4(r.N.x, r.N.y, r.N.z, 1.0f);
+      }
+      if (kp.object_id) kp.object_id[at] = r.object_id;
+    }
+    if (!coh) tile = __shfl_sync(0xffffffffu, next, 0);
+  }
+}
+
+inline cudaError_t upload_probe_order(const int* order16) {
+  return cudaMemcpyToSymbol(c_probe_order, order16, sizeof(int) * 16);
+}
+
+inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4);
+  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel, kThreads, smem);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
+  unsigned ctas = (unsigned)(sm_count * per_sm);
+  const unsigned needed = (num_tiles + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (ctas > needed) ctas = needed;
+  if (ctas < 1) ctas = 1;
+  // how far the work counter advances during this launch (reported through *warps_launched
+  // as "advance - num_tiles", the form rt_render adds back): independent mode = one fetch per
+  // tile + one failing fetch per warp; coherent mode = one per block + one per CTA.
+  if (kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
+  else *warps_launched = ctas * kWarpsPerCta;
+  rt_packet_kernel<<<ctas, kThreads, smem, stream>>>(kp);
+  return cudaGetLastError();
+}
+
+}  // namespace pk
+}  // namespace RT_VARIANT_NS
+}  // namespace rt

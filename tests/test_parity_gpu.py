@@ -51,6 +51,52 @@ def test_config_parity_ieee_variant_is_near_exact(rt_ctx, port_oracle, n):
     assert st["color_max_abs_same_id"] < 1e-3 or st["color_bad"] <= 2, st
 
 
+def _bits_equal(a: dict, b: dict) -> dict:
+    return {k: int((a[k].view(np.uint32) != b[k].view(np.uint32)).sum()) if a[k].dtype == np.float32
+            else int((a[k] != b[k]).sum()) for k in ("color", "position", "normal", "object_id")}
+
+
+FULLISH = {1: (1280, 720), 2: (1920, 1080), 3: (960, 540), 4: (480, 270), 5: (1920, 1080)}
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5])
+def test_packet_kernel_is_bit_identical_to_literal_kernel(rt_ctx, n):
+    """The product (packet) kernel restructures the loops — sign-select slabs, 4-ray shadow
+    packets, BRDF-zero skipping, split sphere/plane arrays — without changing one operation of
+    the geometric or shading chain: in the IEEE build it must reproduce the one-ray-per-lane
+    literal kernel bit for bit, at or near BASELINE's full sizes (a size-independent property)."""
+    w = synthetic.config(n, *FULLISH[n])
+    if n == 4:
+        w.num_samples = 4
+    base = abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32
+    a = render_workload(rt_ctx, w, flags=base)
+    b = render_workload(rt_ctx, w, flags=base | abi.FLAG_LITERAL_KERNEL, bind=False)
+    assert _bits_equal(a, b) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
+
+
+@pytest.mark.parametrize("name", sorted(edge_workloads().keys()))
+def test_packet_kernel_is_bit_identical_on_edge_cases(rt_ctx, name):
+    w = edge_workloads(size=(96, 64))[name]
+    base = abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32
+    a = render_workload(rt_ctx, w, flags=base)
+    b = render_workload(rt_ctx, w, flags=base | abi.FLAG_LITERAL_KERNEL, bind=False)
+    assert _bits_equal(a, b) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}, name
+
+
+def test_fast_packet_kernel_stays_close_to_fast_literal_kernel(rt_ctx):
+    """Fast build: the packet kernel additionally approximates shadow-ray setup (MUFU rcp/rsqrt,
+    root-free sphere occlusion). Those can only flip a shadow sample at an exact silhouette."""
+    for n in (2, 3):
+        w = synthetic.config(n, 960, 540)
+        a = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32)
+        b = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32 | abi.FLAG_LITERAL_KERNEL, bind=False)
+        assert (a["object_id"] != b["object_id"]).sum() == 0
+        assert np.array_equal(a["position"].view(np.uint32), b["position"].view(np.uint32))
+        with np.errstate(invalid="ignore"):
+            bad = (np.abs(a["color"] - b["color"]) > 1e-3).any(axis=-1)
+        assert bad.mean() <= 2e-4, (n, int(bad.sum()))
+
+
 def test_config4_multisample_mean(rt_ctx, port_oracle):
     """C4 at reduced size: exact-sequence test (same Hammersley indices, sequential FP32 sum)."""
     w = synthetic.config(4, 128, 72)
