@@ -229,7 +229,8 @@ rt_status rt_render_host(rt_context* ctx, const rt_frame_params* params,
                          void* h_normal, int32_t* h_object_id);
 
 /* How rt_render_host moves the three images to the host (a tuning knob, not semantics):
- * AUTO = BANDED when every host buffer is pinned (rt_host_alloc / cudaHostRegister), else STAGED. */
+ * AUTO = ZEROCOPY when every host buffer is pinned and device-mapped (rt_host_alloc /
+ * cudaHostRegister: the kernel stores straight into host memory over PCIe), else BANDED. */
 enum { RT_HOST_PATH_AUTO = 0, RT_HOST_PATH_STAGED = 1, RT_HOST_PATH_BANDED = 2, RT_HOST_PATH_ZEROCOPY = 3 };
 rt_status rt_set_host_path(rt_context* ctx, int path);
 

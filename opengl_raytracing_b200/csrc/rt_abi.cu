@@ -438,7 +438,7 @@ rt_status rt_render_host(rt_context* c, const rt_frame_params* p, const void* ob
     return a.type == cudaMemoryTypeHost && a.devicePointer == h;
   };
   const bool all_mapped = mapped(h_color) && mapped(h_position) && mapped(h_normal) && mapped(h_object_id);
-  if (path == RT_HOST_PATH_AUTO) path = all_mapped ? RT_HOST_PATH_BANDED : RT_HOST_PATH_STAGED;
+  if (path == RT_HOST_PATH_AUTO) path = all_mapped ? RT_HOST_PATH_ZEROCOPY : RT_HOST_PATH_BANDED;   // measured: profiles/README.md
   if (path == RT_HOST_PATH_ZEROCOPY && !all_mapped) path = RT_HOST_PATH_STAGED;
   if (path == RT_HOST_PATH_ZEROCOPY) {
     st = rt_render(c, p, h_color, h_position, h_normal, h_object_id, c->stream);
