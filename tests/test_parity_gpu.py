@@ -233,6 +233,39 @@ def test_render_host_matches_device_path(rt_ctx):
     assert np.array_equal(oid, k["object_id"]) and np.array_equal(nrm.astype(np.float32), k["normal"])
 
 
+@pytest.mark.parametrize("path", [abi.HOST_PATH_STAGED, abi.HOST_PATH_BANDED, abi.HOST_PATH_ZEROCOPY])
+def test_render_host_paths_agree_with_pinned_buffers(rt_ctx, path):
+    """rt_render_host into pinned (device-mapped) host memory: the staged, banded and zero-copy
+    routes must deliver the same bytes as the device path."""
+    import ctypes as C
+    w = synthetic.config(2, 640, 360)
+    k = render_workload(rt_ctx, w)
+    H, W = w.height, w.width
+    sizes = {"color": H * W * 16, "position": H * W * 16, "normal": H * W * 8, "oid": H * W * 4}
+    ptr = {}
+    for name, nbytes in sizes.items():
+        p = C.c_void_p(0)
+        assert rt_ctx.lib.rt_host_alloc(C.byref(p), nbytes) == 0
+        C.memset(p, 0xEE, nbytes)
+        ptr[name] = p
+    try:
+        assert rt_ctx.lib.rt_set_host_path(rt_ctx.handle, path) == 0
+        objs, lights = np.ascontiguousarray(w.objects), np.ascontiguousarray(w.lights)
+        st = rt_ctx.lib.rt_render_host(rt_ctx.handle, C.byref(workload_params(w)), objs.ctypes.data, len(objs),
+                                       lights.ctypes.data, len(lights), ptr["color"], ptr["position"], ptr["normal"], ptr["oid"])
+        assert st == 0, rt_ctx.lib.rt_last_error(rt_ctx.handle)
+        def view(name, dtype, shape):
+            return np.frombuffer((C.c_char * sizes[name]).from_address(ptr[name].value), dtype=dtype).reshape(shape)
+        assert np.array_equal(view("color", np.uint32, (H, W, 4)), k["color"].view(np.uint32))
+        assert np.array_equal(view("position", np.uint32, (H, W, 4)), k["position"].view(np.uint32))
+        assert np.array_equal(view("normal", np.float16, (H, W, 4)).astype(np.float32), k["normal"])
+        assert np.array_equal(view("oid", np.int32, (H, W)), k["object_id"])
+    finally:
+        rt_ctx.lib.rt_set_host_path(rt_ctx.handle, abi.HOST_PATH_AUTO)
+        for p in ptr.values():
+            rt_ctx.lib.rt_host_free(p)
+
+
 def test_reference_named_host_mirror(rt_ctx, port_oracle):
     """The ForwardShadingPipeline / SSBO / LightSSBO / RaytracingShader mirror renders the
     default scene like the oracle does (fov 45 from Camera, depth 3, frameCount under TAA)."""
