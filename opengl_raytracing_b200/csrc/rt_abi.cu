@@ -149,7 +149,7 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
     if (o.type == 0) {
       float* r = sph + (size_t)ks * 16;
       box(r, o.bounds);
-      r[12] = o.position[0]; r[13] = o.position[1]; r[14] = o.position[2]; r[15] = o.radius * o.radius;
+      r[12] = o.position[0]; r[13] = o.position[1]; r[14] = o.position[2]; r[15] = o.radius;
       sph_index[ks++] = i;
     } else if (o.type == 1) {
       float* r = pln + (size_t)kp * 32;
@@ -164,6 +164,8 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
       r[20] = forward.x; r[21] = forward.y; r[22] = forward.z; r[23] = 0.f;
       r[24] = o.position[0]; r[25] = o.position[1]; r[26] = o.position[2];
       std::memcpy(&r[27], &i, 4);
+      // conservative bounds for the shadow-job cone test: rectangle bounding radius, |normal|
+      r[28] = std::sqrt(r[15] * r[15] + r[19] * r[19]) * 1.0001f; r[29] = std::sqrt(hdot(nrm, nrm)) * 1.0001f;
       kp++;
     }
   }
@@ -394,7 +396,7 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   // (the packet blob is staged for the full scene), or the scene does not fit shared memory.
   const bool full_scene = p->num_objects == c->n_obj && p->num_lights == c->n_lights;
   const bool use_packet = !(p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) && full_scene && c->pk_float4s > 0 &&
-                          c->pk_float4s * sizeof(float4) <= (size_t)c->max_smem_optin - 1024;
+                          c->pk_float4s * sizeof(float4) + 24 * 256 * 2 <= (size_t)c->max_smem_optin - 1024;
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);

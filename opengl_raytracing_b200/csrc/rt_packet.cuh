@@ -66,9 +66,10 @@ __device__ __forceinline__ f3 normalize_shadow(f3 a) { return a * rsqrtf(dot3(a,
 
 // ---------------------------------------------------------------- shared-memory scene
 // Byte layout, built on the host by stage_scene_packet() (rt_abi.cu):
-//   sphere record  64 B : x(lo,hi,hi,lo) y(lo,hi,hi,lo) z(lo,hi,hi,lo) (cx,cy,cz,r*r)
+//   sphere record  64 B : x(lo,hi,hi,lo) y(lo,hi,hi,lo) z(lo,hi,hi,lo) (cx,cy,cz,r)
 //   plane record  128 B : the same 48-B box, (n.xyz, size.x/2) (right.xyz, size.y/2)
-//                         (forward.xyz, 0) (position.xyz, original index bits) + 16 B pad
+//                         (forward.xyz, 0) (position.xyz, original index bits)
+//                         (bounding radius of the rectangle, |normal|, 0, 0)
 //   sphere_index   4 B  : original object index of each sphere slot
 // lo/hi are sorted per axis on the host (the shader's min/max make the test symmetric in them).
 constexpr int kSphereBytes = 64, kPlaneBytes = 128;
@@ -99,11 +100,11 @@ __device__ __forceinline__ bool dir_regular(f3 d, float a) {
   return fmin3(fabsf(d.x), fabsf(d.y), fabsf(d.z)) > 1.0e-30f && a < 1.0e30f;   // a = dot(d,d): NaN/inf fail
 }
 
-// intersectSphere (glsl:105-118), a = dot(d,d) hoisted; sp = (centre, r*r).
+// intersectSphere (glsl:105-118), a = dot(d,d) hoisted; sp = (centre, r).
 __device__ __forceinline__ bool sphere_t(float4 sp, f3 o, f3 d, float a, float& t) {
   const f3 oc = o - xyz(sp);
   const float b = 2.0f * dot3(oc, d);
-  const float c = dot3(oc, oc) - sp.w;
+  const float c = dot3(oc, oc) - sp.w * sp.w;
   const float disc = b * b - 4.0f * a * c;
   if (disc < 0.0f) return false;
   t = div_ieee(-b - sqrt_ieee(disc), 2.0f * a);
@@ -147,17 +148,16 @@ __device__ __forceinline__ int hit_object_index(const Scene& s, int code) {
   return code < s.ns ? lds32i(s.sph_index + 4u * (unsigned)code) : lds32i(s.pln + (unsigned)(code - s.ns) * kPlaneBytes + 108u);
 }
 
-// One ray against the whole scene. ANY: stop at the first hit with 0 < t < lim (shadow rays;
-// `hit && closestT < L` of glsl:388-392 <=> such a hit exists). Otherwise closest hit with the
-// shader's tie rule. GENERIC: explicit min/max per axis (any direction, incl. NaN and 0).
-template <bool ANY, bool GENERIC>
-__device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, float a, float lim) {
+// Closest hit of one ray over the whole scene, the shader's tie rule (glsl:155-196).
+// GENERIC: explicit min/max per axis (any direction, incl. NaN and 0).
+template <bool GENERIC>
+__device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, float a) {
   // per-axis running addresses of the (near,far) pair this ray's sign selects
   saddr ax = s.sph + ((!GENERIC && d.x < 0.0f) ? 8u : 0u);
   saddr ay = s.sph + ((!GENERIC && d.y < 0.0f) ? 24u : 16u);
   saddr az = s.sph + ((!GENERIC && d.z < 0.0f) ? 40u : 32u);
   const float nox = -o.x, noy = -o.y, noz = -o.z;
-  Hit h; h.code = -1; h.t = ANY ? lim : s.maxd;
+  Hit h; h.code = -1; h.t = s.maxd;
   auto slab = [&](unsigned off) -> bool {
     const float2 X = mul2(add2(lds64(ax + off), dup2(nox)), dup2(inv.x));
     const float2 Y = mul2(add2(lds64(ay + off), dup2(noy)), dup2(inv.y));
@@ -172,24 +172,21 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, flo
     }
     return tmax >= tmin && tmin < s.maxd && tmax > 0.0f;      // glsl:102
   };
-  auto sphere = [&](int k) -> bool {                           // true: ANY hit found
+  auto sphere = [&](int k) {
     float t;
     if (sphere_t(lds128(s.sph + (unsigned)k * kSphereBytes + 48u), o, d, a, t) && t < h.t) {   // t > 0 checked in sphere_t
-      h.code = k;
-      if (ANY) return true;
-      h.t = t;
+      h.code = k; h.t = t;
     }
-    return false;
   };
   int k = 0;
   for (; k + 2 <= s.ns; k += 2, ax += 2 * kSphereBytes, ay += 2 * kSphereBytes, az += 2 * kSphereBytes) {
     const bool p0 = slab(0u), p1 = slab((unsigned)kSphereBytes);
     if (p0 | p1) {
-      if (p0 && sphere(k)) return h;
-      if (p1 && sphere(k + 1)) return h;
+      if (p0) sphere(k);
+      if (p1) sphere(k + 1);
     }
   }
-  if (k < s.ns && slab(0u) && sphere(k)) return h;
+  if (k < s.ns && slab(0u)) sphere(k);
   const unsigned tail = (unsigned)(s.ns - k) * kSphereBytes;   // s.pln follows the sphere records
   ax += tail; ay += tail; az += tail;
   saddr rec = s.pln;
@@ -197,100 +194,188 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, flo
     if (!slab(0u)) continue;
     float t;
     if (!plane_t(rec, o, d, t) || !(t > 0.0f)) continue;
-    if (ANY) {
-      if (t < h.t) { h.code = s.ns + j; return h; }
-    } else if (t < h.t || (t == h.t && h.code >= 0 && lds32i(rec + 108u) < hit_object_index(s, h.code))) {
+    if (t < h.t || (t == h.t && h.code >= 0 && lds32i(rec + 108u) < hit_object_index(s, h.code))) {
       h.t = t; h.code = s.ns + j;
     }
   }
-  if (ANY) h.code = -1;
   return h;
 }
 
-// The cold variants live behind calls so the hot loops stay small in the instruction cache.
+// The cold variant lives behind a call so the hot loop stays small in the instruction cache.
 __device__ __noinline__ Hit trace_closest_generic(const Scene& s, f3 o, f3 d, f3 inv, float a) {
-  return trace_one<false, true>(s, o, d, inv, a, 0.0f);
-}
-__device__ __noinline__ bool trace_any_one(const Scene& s, f3 o, f3 d, float lim) {
-  const float a = dot3(d, d);
-  const f3 inv = mk3(rcp_shadow(d.x), rcp_shadow(d.y), rcp_shadow(d.z));
-  if (dir_regular(d, a)) return trace_one<true, false>(s, o, d, inv, a, lim).code >= 0;
-  const f3 inv_ieee = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
-  return trace_one<true, true>(s, o, d, inv_ieee, a, lim).code >= 0;
+  return trace_one<true>(s, o, d, inv, a);
 }
 
-// Closest hit for primary / bounce / SSS rays (glsl:155-196). IEEE 1/dir in both builds: the
-// hit set of these rays feeds P and N.
+// Closest hit for primary / bounce / SSS rays. IEEE 1/dir in both builds: the hit set of these
+// rays feeds P and N.
 __device__ __forceinline__ Hit trace_closest(const Scene& s, f3 o, f3 d) {
   const f3 inv = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
   const float a = dot3(d, d);
   if (!dir_regular(d, a)) return trace_closest_generic(s, o, d, inv, a);
-  return trace_one<false, false>(s, o, d, inv, a, 0.0f);
+  return trace_one<false>(s, o, d, inv, a);
 }
 
-// 4 shadow rays with a common origin. Returns the mask of rays that hit something with
-// 0 < t < lim. Rays outside `active` must carry a copy of an active ray's direction.
-__device__ __forceinline__ unsigned trace_any_packet(const Scene& s, f3 o, const f3 (&d)[4], unsigned active, float lim) {
+// ---------------------------------------------------------------- shadow jobs: cone culling
+// All shadow rays of one (shading point, light) — 16 PCSS probes and/or the PCF samples — start
+// at the same origin and lie in a cone around lightDir: a probe is normalize(L + 2*rv*ss*(1,1,1))
+// (glsl:408-409, |rv| <= 1), a PCF sample is L + fs*(rx*T + ry*B) with rx,ry in [0,1), |T| = 1,
+// |B| <= 1 (glsl:366-378); for |L| = 1 and |delta| <= e < 1 the angle to L has sin <= e.
+// An object no ray of that cone can touch cannot occlude, whatever its AABB says (a hit needs the
+// AABB test AND the primitive test), so the job first scans the scene once with a CONSERVATIVE
+// cone-vs-bounding-sphere test and the ray packets then visit only the survivors, with the exact
+// per-ray tests. No survivor: every probe / sample is unoccluded, the factor is exactly 1.
+// Conservative: sin is over-, cos under-estimated, radii are inflated by 1e-3, and the squared
+// comparison carries a 4e-6*|v|^2 slack (40x the rounding of d2 - along^2, and above the
+// 1e-7*|v|^2 by which the shader's own discriminant can report a grazing hit).
+constexpr int kCandCap = 24;          // per-thread candidate list (u16 codes) in shared memory
+
+struct Cone { f3 L; float s, c2, far; };        // axis, sin bound, cos^2 bound, far = lim*(1+e)
+struct Cands { saddr base; int n; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test)
+
+__device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 center, float r) {
+  const f3 v = center - o;
+  const float along = fmaf(v.z, c.L.z, fmaf(v.y, c.L.y, v.x * c.L.x));
+  const float d2 = fmaf(v.z, v.z, fmaf(v.y, v.y, v.x * v.x));
+  const float rr = r * 1.001f;
+  const float q = fmaf(along, c.s, rr);                     // r' + along*sin
+  const float lhs = fmaf(-along, along, d2) * c.c2;         // perp^2 * cos^2
+  const float rhs = fmaf(d2, 4.0e-6f, q * q);
+  return q < 0.0f || lhs > rhs || along - rr > c.far;      // any NaN: not culled
+}
+__device__ __forceinline__ bool cone_misses_plane(const Cone& c, f3 o, saddr rec) {
+  const float4 pn = lds128(rec + 48u), pp = lds128(rec + 96u), pb = lds128(rec + 112u);
+  const f3 n = xyz(pn);
+  const float s0 = dot3(xyz(pp) - o, n);                    // the numerator of glsl:127, same operations
+  const float nl = fmaf(n.z, c.L.z, fmaf(n.y, c.L.y, n.x * c.L.x));
+  const float slack = pb.y * (c.s + 1.0e-5f);               // |n.delta| <= |n| e (+ rounding)
+  // every denominator n.d has one strict sign and the numerator the opposite (or zero): t <= 0
+  if ((s0 <= 0.0f && nl > slack) || (s0 >= 0.0f && nl < -slack)) return true;
+  return cone_misses_sphere(c, o, xyz(pp), pb.x);
+}
+
+__device__ __forceinline__ saddr record_of(const Scene& s, int code) {
+  return code < s.ns ? s.sph + (unsigned)code * kSphereBytes : s.pln + (unsigned)(code - s.ns) * kPlaneBytes;
+}
+__device__ __forceinline__ int cand_code(const Cands& cd, int i) {
+  if (!cd.list) return i;
+  unsigned short v; asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(cd.base + (unsigned)i * (kThreads * 2u)));
+  return (int)v;
+}
+
+// One scan of the scene per shadow job. Returns the candidate set for the job's packets.
+__device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base, bool cone_ok, const Cone& cone, f3 o) {
+  Cands cd; cd.base = cand_base; cd.n = s.ns + s.np; cd.list = false; cd.prefilter = false;
+  if (!cone_ok) return cd;
+  int n = 0;
+  saddr rec = s.sph;
+#pragma unroll 2
+  for (int k = 0; k < s.ns; ++k, rec += kSphereBytes) {
+    const float4 sp = lds128(rec + 48u);
+    if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
+    if (n < kCandCap) asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)n * (kThreads * 2u)), "h"((unsigned short)k) : "memory");
+    ++n;
+  }
+  for (int j = 0; j < s.np; ++j, rec += kPlaneBytes) {
+    if (cone_misses_plane(cone, o, rec)) continue;
+    if (n < kCandCap) asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)n * (kThreads * 2u)), "h"((unsigned short)(s.ns + j)) : "memory");
+    ++n;
+  }
+  if (n <= kCandCap) { cd.list = true; cd.n = n; }
+  else cd.prefilter = true;                                  // too many survivors: full scan, cone test inline
+  return cd;
+}
+
+// One shadow ray against the job's candidates (packets whose rays disagree in sign, or carry an
+// irregular direction, fall back to this ray by ray).
+__device__ __noinline__ bool trace_any_one(const Scene& s, const Cands& cd, const Cone& cone, f3 o, f3 d, float lim) {
+  const float a = dot3(d, d);
+  const bool regular = dir_regular(d, a);
+  const f3 inv = regular ? mk3(rcp_shadow(d.x), rcp_shadow(d.y), rcp_shadow(d.z)) : mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
+  const unsigned ox = (regular && d.x < 0.0f) ? 8u : 0u, oy = (regular && d.y < 0.0f) ? 24u : 16u, oz = (regular && d.z < 0.0f) ? 40u : 32u;
+#pragma unroll 1
+  for (int i = 0; i < cd.n; ++i) {
+    const int code = cand_code(cd, i);
+    const saddr rec = record_of(s, code);
+    if (cd.prefilter && (code < s.ns ? cone_misses_sphere(cone, o, xyz(lds128(rec + 48u)), lds32(rec + 60u)) : cone_misses_plane(cone, o, rec))) continue;
+    const float2 X = mul2(add2(lds64(rec + ox), dup2(-o.x)), dup2(inv.x));
+    const float2 Y = mul2(add2(lds64(rec + oy), dup2(-o.y)), dup2(inv.y));
+    const float2 Z = mul2(add2(lds64(rec + oz), dup2(-o.z)), dup2(inv.z));
+    float tmin, tmax;
+    if (regular) { tmin = fmax3(X.x, Y.x, Z.x); tmax = fmin3(X.y, Y.y, Z.y); }
+    else {
+      tmin = fmax3(fminf(X.x, X.y), fminf(Y.x, Y.y), fminf(Z.x, Z.y));
+      tmax = fmin3(fmaxf(X.x, X.y), fmaxf(Y.x, Y.y), fmaxf(Z.x, Z.y));
+    }
+    if (!(tmax >= tmin && tmin < s.maxd && tmax > 0.0f)) continue;
+    float t;
+    const bool hit = code < s.ns ? sphere_t(lds128(rec + 48u), o, d, a, t) : plane_t(rec, o, d, t);
+    if (hit && t > 0.0f && t < lim) return true;
+  }
+  return false;
+}
+
+// 4 shadow rays with a common origin against the job's candidates. Returns the mask of rays that
+// hit something with 0 < t < lim. Rays of the packet that agree in all three direction signs are
+// traced together (one traversal per sign group: normally one, two when a PCSS packet straddles an
+// axis); a ray with a NaN direction cannot hit anything (every comparison is false); a ray with a
+// zero / denormal / infinite component goes through the generic single-ray routine.
+__device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands& cd, const Cone& cone, f3 o,
+                                                     const f3 (&d)[4], unsigned active, float lim) {
   float a[4];
   float2 ivx[4], ivy[4], ivz[4];
-  bool regular = true;
-  unsigned sx = 0u, sy = 0u, sz = 0u;
+  unsigned signs = 0u, remaining = active, occ = 0u;       // signs: 3 bits per ray
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     a[r] = dot3(d[r], d[r]);
-    regular = regular && dir_regular(d[r], a[r]);
-    sx |= __float_as_uint(d[r].x) ^ __float_as_uint(d[0].x);
-    sy |= __float_as_uint(d[r].y) ^ __float_as_uint(d[0].y);
-    sz |= __float_as_uint(d[r].z) ^ __float_as_uint(d[0].z);
+    signs |= ((__float_as_uint(d[r].x) >> 31) | ((__float_as_uint(d[r].y) >> 31) << 1) | ((__float_as_uint(d[r].z) >> 31) << 2)) << (3 * r);
     ivx[r] = dup2(rcp_shadow(d[r].x)); ivy[r] = dup2(rcp_shadow(d[r].y)); ivz[r] = dup2(rcp_shadow(d[r].z));   // FMUL2 takes the scalar broadcast form
-  }
-  if (!regular || ((sx | sy | sz) >> 31)) {            // mixed signs or an irregular direction: ray by ray
-    unsigned occ = 0u;
-#pragma unroll 1
-    for (int r = 0; r < 4; ++r) {
-      if (!((active >> r) & 1u)) continue;
-      const f3 dr = r == 0 ? d[0] : (r == 1 ? d[1] : (r == 2 ? d[2] : d[3]));
-      if (trace_any_one(s, o, dr, lim)) occ |= 1u << r;
+    if (((active >> r) & 1u) && !dir_regular(d[r], a[r])) {
+      remaining &= ~(1u << r);
+      if (a[r] == a[r] && trace_any_one(s, cd, cone, o, d[r], lim)) occ |= 1u << r;     // a is NaN iff a component is
     }
-    return occ;
   }
-  saddr ax = s.sph + (d[0].x < 0.0f ? 8u : 0u), ay = s.sph + (d[0].y < 0.0f ? 24u : 16u), az = s.sph + (d[0].z < 0.0f ? 40u : 32u);
   const float nox = -o.x, noy = -o.y, noz = -o.z;
-  unsigned occ = 0u;
-  bool pass[4];
-  auto slabs = [&]() -> bool {
-    const float2 X = add2(lds64(ax), dup2(nox)), Y = add2(lds64(ay), dup2(noy)), Z = add2(lds64(az), dup2(noz));
-    bool any = false;
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const float2 tx = mul2(X, ivx[r]), ty = mul2(Y, ivy[r]), tz = mul2(Z, ivz[r]);
-      const float tmin = fmax3(tx.x, ty.x, tz.x), tmax = fmin3(tx.y, ty.y, tz.y);
-      pass[r] = tmax >= tmin && tmin < s.maxd && tmax > 0.0f;
-      any = any || pass[r];
-    }
-    return any;
-  };
-  saddr rec = s.sph;
 #pragma unroll 1
-  for (int k = 0; k < s.ns; ++k, rec += kSphereBytes, ax += kSphereBytes, ay += kSphereBytes, az += kSphereBytes) {
-    if (!slabs()) continue;
-    const float4 sp = lds128(rec + 48u);
-    const f3 oc = o - xyz(sp);
-    const float cc = dot3(oc, oc) - sp.w;
+  while (remaining) {
+    const unsigned lead = (signs >> (3 * (__ffs(remaining) - 1))) & 7u;
+    unsigned group = 0u;
 #pragma unroll
-    for (int r = 0; r < 4; ++r)
-      if (pass[r] && !((occ >> r) & 1u) && sphere_any(oc, cc, d[r], a[r], lim)) occ |= 1u << r;
-    if ((occ & active) == active) return occ;
-  }
+    for (int r = 0; r < 4; ++r) if (((signs >> (3 * r)) & 7u) == lead) group |= 1u << r;
+    group &= remaining;
+    remaining &= ~group;
+    const unsigned ox = (lead & 1u) ? 8u : 0u, oy = (lead & 2u) ? 24u : 16u, oz = (lead & 4u) ? 40u : 32u;
 #pragma unroll 1
-  for (int j = 0; j < s.np; ++j, rec += kPlaneBytes, ax += kPlaneBytes, ay += kPlaneBytes, az += kPlaneBytes) {
-    if (!slabs()) continue;
+    for (int i = 0; i < cd.n; ++i) {
+      const int code = cand_code(cd, i);
+      const saddr rec = record_of(s, code);
+      const bool is_sphere = code < s.ns;
+      if (cd.prefilter && (is_sphere ? cone_misses_sphere(cone, o, xyz(lds128(rec + 48u)), lds32(rec + 60u)) : cone_misses_plane(cone, o, rec))) continue;
+      const float2 X = add2(lds64(rec + ox), dup2(nox)), Y = add2(lds64(rec + oy), dup2(noy)), Z = add2(lds64(rec + oz), dup2(noz));
+      bool pass[4], any = false;
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      float t;
-      if (pass[r] && !((occ >> r) & 1u) && plane_t(rec, o, d[r], t) && t > 0.0f && t < lim) occ |= 1u << r;
+      for (int r = 0; r < 4; ++r) {
+        const float2 tx = mul2(X, ivx[r]), ty = mul2(Y, ivy[r]), tz = mul2(Z, ivz[r]);
+        const float tmin = fmax3(tx.x, ty.x, tz.x), tmax = fmin3(tx.y, ty.y, tz.y);
+        pass[r] = tmax >= tmin && tmin < s.maxd && tmax > 0.0f && ((group >> r) & 1u);
+        any = any || pass[r];
+      }
+      if (!any) continue;
+      if (is_sphere) {
+        const float4 sp = lds128(rec + 48u);
+        const f3 oc = o - xyz(sp);
+        const float cc = dot3(oc, oc) - sp.w * sp.w;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          if (pass[r] && !((occ >> r) & 1u) && sphere_any(oc, cc, d[r], a[r], lim)) occ |= 1u << r;
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          float t;
+          if (pass[r] && !((occ >> r) & 1u) && plane_t(rec, o, d[r], t) && t > 0.0f && t < lim) occ |= 1u << r;
+        }
+      }
+      if ((occ & group) == group) break;                    // every ray of the group is occluded
     }
-    if ((occ & active) == active) return occ;
   }
   return occ;
 }
@@ -322,7 +407,7 @@ __device__ __forceinline__ Mat load_material(const Scene& s, int index) {
 // calculateShadow (glsl:442-455) for shadowType 1 (pcfShadow, glsl:342-397) and 2 (pcssShadow,
 // glsl:400-440 = "fully lit unless one of 16 fixed probes is blocked, else PCF"). Probes and PCF
 // samples run through ONE packet site: jobs [0,nprobe) are probes, [nprobe,nprobe+pcf) samples.
-__device__ __forceinline__ float shadow_packets(const Scene& s, float noise_r, f3 origin, const LightRec& light,
+__device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
                                                 f3 lightDir, float lightDistance) {
   const int nprobe = light.shadowType == 2 ? 16 : 0;
   const int total = nprobe + (light.pcfSamples > 0 ? light.pcfSamples : 0);
@@ -334,6 +419,17 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, float noise_r, f
   const float lim_light = lightDistance > s.maxd ? s.maxd : lightDistance;
   const float lim_pcf = (light.type == 0 || light.type == 2) ? lim_light : s.maxd;   // glsl:388-392
   const float lim_probe = light.type != 1 ? lim_light : s.maxd;                      // glsl:419-423
+  // the job's cone (see "shadow jobs: cone culling"): e bounds |direction - lightDir|
+  const float e_pcf = 2.0f * fabsf(filterSize), e_probe = nprobe ? 3.4642f * fabsf(searchSize) : 0.0f;
+  Cone cone;
+  cone.L = lightDir;
+  cone.s = fmaxf(e_pcf, e_probe) * 1.01f + 1.0e-5f;
+  cone.c2 = (1.0f - cone.s * cone.s) * 0.999f;
+  cone.far = fmaxf(lim_pcf, lim_probe) * (1.0f + cone.s) * 1.0001f;              // NaN limits: fmaxf keeps the other
+  const float ll = dot3(lightDir, lightDir);
+  const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
+  const Cands cd = scan_candidates(s, cand_base, cone_ok, cone, origin);
+  if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
   int unoccluded = 0;
   int j = 0;
   while (j < total) {
@@ -361,7 +457,7 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, float noise_r, f
         d[r] = d[0];
       }
     }
-    const unsigned occ = trace_any_packet(s, origin, d, active, probing ? lim_probe : lim_pcf) & active;
+    const unsigned occ = trace_any_packet(s, cd, cone, origin, d, active, probing ? lim_probe : lim_pcf) & active;
     if (probing) {
       if (occ) { j = nprobe; continue; }                 // a blocker exists: go to the PCF phase
       j += 4;
@@ -398,7 +494,7 @@ __device__ __forceinline__ void phase_sync(bool coh) { if (coh) __syncthreads();
 // computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
 // lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
 // Every lane of the CTA walks the light loop (lit = this lane has a surface to shade).
-__device__ __forceinline__ f3 compute_lighting(const Scene& s, bool coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
+__device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, bool coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
   f3 Lo = mk3(0.0f, 0.0f, 0.0f);
   const f3 shadow_origin = P + N * 0.001f;               // glsl:381, :412
 #pragma unroll 1
@@ -433,7 +529,7 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, bool coh, bool li
     if (brdf.x == 0.0f && brdf.y == 0.0f && brdf.z == 0.0f && (!sampled || light.pcfSamples > 0)) continue;
     float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
     if (light.shadowType == 0) shadowFactor = 1.0f;
-    else if (sampled) shadowFactor = shadow_packets(s, noise_r, shadow_origin, light, lightDir, lightDistance);
+    else if (sampled) shadowFactor = shadow_packets(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
     Lo = Lo + brdf * shadowFactor;
   }
   if (lit && mat.subsurfaceScatter > 0.0f) Lo = Lo + subsurface(s, P, N, mat);
@@ -446,7 +542,7 @@ struct PixelResult { f3 color, P, N; int object_id; };
 // One invocation of the shader's main() per lane. Whole warps (coh: the whole CTA) call this
 // together; `alive` = this lane still has a path to extend (false from the start for lanes
 // outside the image). The bounce loop ends when no lane of the warp / CTA is alive.
-__device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, bool coh,
+__device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, saddr cand_base, bool coh,
                                                    bool alive, unsigned px, unsigned py, int frame_count) {
   const rt_frame_params& fp = kp.fp;
   const float noise_r = fetch_noise(tx, (float)(px + (unsigned)frame_count) * fp.noise_scale[0],
@@ -495,7 +591,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
         out.P = P; out.N = N; out.object_id = index;
       }
     }
-    const f3 Lo = compute_lighting(s, coh, lit, noise_r, P, N, mat, V);
+    const f3 Lo = compute_lighting(s, cand_base, coh, lit, noise_r, P, N, mat, V);
     if (!lit) continue;
     out.color = out.color + throughput * Lo;
 
@@ -551,6 +647,8 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(co
   s.material = sc.material;
   s.ns = sc.pk_num_spheres; s.np = sc.pk_num_planes; s.nl = sc.num_lights;
   s.maxd = fp.max_ray_distance;
+  // per-thread candidate list behind the scene image: entry i of thread t at +(i*kThreads + t)*2
+  const saddr cand_base = base + (unsigned)sc.pk_float4s * 16u + threadIdx.x * 2u;
 
   Textures tx;
   tx.sky = sc.sky; tx.sky_tex = sc.sky_tex; tx.sky_size = sc.sky_size;
@@ -600,7 +698,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(co
     PixelResult r;                                       // position/normal/id: those of sample 0
 #pragma unroll 1
     for (int sidx = 0; sidx < nsamp; ++sidx) {           // colour: sequential FP32 sum over samples
-      const PixelResult r2 = shade_pixel(kp, s, tx, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
+      const PixelResult r2 = shade_pixel(kp, s, tx, cand_base, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
       if (sidx == 0) r = r2;
       else r.color = r.color + r2.color;
     }
@@ -632,7 +730,7 @@ inline cudaError_t upload_probe_order(const int* order16) {
 }
 
 inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
-  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4);
+  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
   cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
