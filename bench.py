@@ -206,6 +206,8 @@ def run_ours(args) -> None:
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     w = workload_for(args)
@@ -221,7 +223,7 @@ def run_ours(args) -> None:
         params = workload_params(w, flags=flags, row_begin=ra, row_end=rb)
         scaling, par = "strong", f"row tiles x{world}, gathered to rank 0"
     elif world > 1:
-        params = workload_params(w, flags=flags | abi.FLAG_ACCUMULATE, frame_count=w.frame_count + rank * ns)
+        params = workload_params(w, flags=flags | abi.FLAG_SUM_SAMPLES, frame_count=w.frame_count + rank * ns)
         scaling, par = "weak", f"sample ranges x{world} ({ns} spp per rank), NCCL reduce to rank 0"
     else:
         params = workload_params(w, flags=flags)
@@ -235,7 +237,7 @@ def run_ours(args) -> None:
 
     # ---- reference-literal op counts for THIS rank's work (untimed, counter variant)
     pc = abi.FrameParams.from_buffer_copy(params)
-    pc.flags = (params.flags | abi.FLAG_COUNTERS) & ~abi.FLAG_ACCUMULATE
+    pc.flags = (params.flags | abi.FLAG_COUNTERS) & ~(abi.FLAG_ACCUMULATE | abi.FLAG_SUM_SAMPLES)
     ctx.counters(reset=True)
     ctx.render(pc, color, None, None, None, stream.cuda_stream)
     counters = ctx.counters(reset=True)
@@ -308,7 +310,7 @@ def run_ours(args) -> None:
         h[name] = p
     objs = np.ascontiguousarray(w.objects); lights = np.ascontiguousarray(w.lights)
     pe = abi.FrameParams.from_buffer_copy(params)
-    pe.flags = params.flags & ~abi.FLAG_ACCUMULATE
+    pe.flags = params.flags & ~(abi.FLAG_ACCUMULATE | abi.FLAG_SUM_SAMPLES)
     assert ctx.lib.rt_set_host_path(ctx.handle, args.host_path) == 0
     def e2e_step():
         st = ctx.lib.rt_render_host(ctx.handle, abi.C.byref(pe), objs.ctypes.data, len(objs), lights.ctypes.data, len(lights),

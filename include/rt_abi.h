@@ -123,6 +123,7 @@ typedef enum rt_status {
 #define RT_FLAG_SKYBOX_HW       0x04u /* miss path through the CUDA cubemap texture object (HW filter) */
 #define RT_FLAG_COUNTERS        0x08u /* accumulate the reference-literal op counters (rt_get_counters)*/
 #define RT_FLAG_ACCUMULATE      0x10u /* colour += instead of = (sample-range partial sums) */
+#define RT_FLAG_SUM_SAMPLES     0x40u /* colour = plain sum over num_samples (no 1/n): one partial per rank */
 #define RT_FLAG_LITERAL_KERNEL  0x20u /* one-ray-per-lane literal kernel instead of the packet kernel   */
 
 /* == the shader's uniforms (shader/raytracingCs.glsl:72-89) + the compile-time constants

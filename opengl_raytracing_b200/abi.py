@@ -20,6 +20,7 @@ FLAG_SKYBOX_HW = 0x04
 FLAG_COUNTERS = 0x08
 FLAG_ACCUMULATE = 0x10
 FLAG_LITERAL_KERNEL = 0x20
+FLAG_SUM_SAMPLES = 0x40
 HOST_PATH_AUTO, HOST_PATH_STAGED, HOST_PATH_BANDED, HOST_PATH_ZEROCOPY = range(4)
 
 COUNTER_NAMES = [

@@ -235,7 +235,7 @@ rt_status rt_create(rt_context** out, int cuda_device) {
     for (int j = i; j > 0 && h3t[order[j]] < h3t[order[j - 1]]; --j) { int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t; }
   if ((e = rt::upload_tables_fast(h2, h3t, order)) != cudaSuccess) return bail(e);
   if ((e = rt::upload_tables_parity(h2, h3t, order)) != cudaSuccess) return bail(e);
-  if (const char* e2 = getenv("RT_PK_COHERENT")) c->coherent_override = atoi(e2) ? 1 : 0;
+  if (const char* e2 = getenv("RT_PK_COHERENT")) c->coherent_override = atoi(e2);
   *out = c;
   return RT_OK;
 }
@@ -389,19 +389,20 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   kp.tile_counter = c->d_tile_counter; kp.tile_base = c->tile_base;
   kp.tiles_x = (unsigned)((p->width + 7) / 8);
   kp.tiles_y = (unsigned)((p->row_end - p->row_begin + 3) / 4);
-  kp.blocks_x = (kp.tiles_x + 3) / 4; kp.blocks_y = (kp.tiles_y + 1) / 2;
+  const unsigned bty = (unsigned)rt::packet_block_tiles_y();
+  kp.blocks_x = (kp.tiles_x + 3) / 4; kp.blocks_y = (kp.tiles_y + bty - 1) / bty;
   kp.counters = c->d_counters;
   // Kernel selection: the packet kernel (rt_packet.cuh) unless the caller asks for the literal
   // one (counters need its reference-literal loops), renders a prefix of the uploaded arrays
   // (the packet blob is staged for the full scene), or the scene does not fit shared memory.
   const bool full_scene = p->num_objects == c->n_obj && p->num_lights == c->n_lights;
   const bool use_packet = !(p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) && full_scene && c->pk_float4s > 0 &&
-                          c->pk_float4s * sizeof(float4) + 24 * 256 * 2 <= (size_t)c->max_smem_optin - 1024;
+                          c->pk_float4s * sizeof(float4) + 24 * 1024 * 2 <= (size_t)c->max_smem_optin - 1024;
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);
   // with long loops the barrier imbalance costs more than the fetch locality gains.
-  sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : (c->pk_spheres + c->pk_planes <= 48 ? 1 : 0);
+  sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : (c->pk_spheres + c->pk_planes <= 48 ? 3 : 0);
   unsigned warps = 0;
   const bool par = (p->flags & RT_FLAG_PARITY_MATH) != 0u;
   cudaError_t e;

@@ -69,6 +69,7 @@ size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights);
 cudaError_t launch_render_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
 cudaError_t launch_render_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
 
+int packet_block_tiles_y();   // CTA block height in tiles (coherent mode), fixed at build time
 cudaError_t launch_packet_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
 cudaError_t launch_packet_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched);
 

@@ -459,7 +459,7 @@ __global__ void __launch_bounds__(kThreads) rt_render_kernel(const __grid_consta
         if (fp.flags & RT_FLAG_ACCUMULATE) {             // partial sums for sample-range sharding
           const float4 old = kp.color[at];
           c = make_float4(old.x + c.x, old.y + c.y, old.z + c.z, 1.0f);
-        } else if (ns > 1) {
+        } else if (ns > 1 && !(fp.flags & RT_FLAG_SUM_SAMPLES)) {
           c = make_float4(c.x * inv_ns, c.y * inv_ns, c.z * inv_ns, 1.0f);
         }
         kp.color[at] = c;

@@ -9,12 +9,13 @@ namespace rt {
 cudaError_t launch_render_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   return fast::launch_render(kp, sm_count, stream, warps_launched);
 }
+int packet_block_tiles_y() { return fast::pk::kBlockTilesY; }
 cudaError_t launch_packet_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   return fast::pk::launch_packet(kp, sm_count, stream, warps_launched);
 }
 cudaError_t upload_tables_fast(const float* halton2, const float* halton3, const int* probe_order) {
   cudaError_t e = fast::upload_tables(halton2, halton3);
   if (e != cudaSuccess) return e;
-  return fast::pk::upload_probe_order(probe_order);
+  return fast::pk::upload_probe_order(halton3, probe_order);
 }
 }  // namespace rt

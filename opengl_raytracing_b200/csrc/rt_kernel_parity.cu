@@ -15,6 +15,6 @@ cudaError_t launch_packet_parity(const KernelParams& kp, int sm_count, cudaStrea
 cudaError_t upload_tables_parity(const float* halton2, const float* halton3, const int* probe_order) {
   cudaError_t e = parity::upload_tables(halton2, halton3);
   if (e != cudaSuccess) return e;
-  return parity::pk::upload_probe_order(probe_order);
+  return parity::pk::upload_probe_order(halton3, probe_order);
 }
 }  // namespace rt

@@ -67,7 +67,10 @@ struct Textures {
   const unsigned char* noise; int noise_w, noise_h;
 };
 
-__device__ __forceinline__ int wrap_repeat(int i, int n) { int m = i % n; return m < 0 ? m + n : m; }
+__device__ __forceinline__ int wrap_repeat(int i, int n) {
+  if ((n & (n - 1)) == 0) return i & (n - 1);            // power of two (the usual 1024): same value as the modulo
+  int m = i % n; return m < 0 ? m + n : m;
+}
 
 // texture(blueNoiseTex, uv).r — GL_R8, REPEAT, LINEAR with FP32 weights
 // (src/ForwardShadingPipeline.cpp:39-49); unbound -> 0. .g is always 0.

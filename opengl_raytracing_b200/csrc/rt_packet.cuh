@@ -28,14 +28,19 @@ namespace rt {
 namespace RT_VARIANT_NS {
 namespace pk {
 
-constexpr int kWarpsPerCta = 8;
+#ifndef RT_PK_WARPS
+#define RT_PK_WARPS 8
+#endif
+constexpr int kWarpsPerCta = RT_PK_WARPS;
 constexpr int kThreads = kWarpsPerCta * 32;
 constexpr int kTileW = 8, kTileH = 4;            // one warp = 8x4 pixels
+constexpr int kBlockTilesX = 4, kBlockTilesY = kWarpsPerCta / 4;   // coherent mode: CTA block = 32 x (4*warps/4) pixels
 
-// PCSS probe indices sorted by their offset halton3(i)*2-1: consecutive probes lie next to
-// each other on the line lightDir + rv*(1,1,1)*2s, so a packet of 4 rarely straddles a sign
+// The 16 PCSS probe offsets rv = halton3(i)*2-1 (glsl:408), sorted: consecutive probes lie next
+// to each other on the line lightDir + rv*(1,1,1)*2s, so a packet of 4 rarely straddles a sign
 // change. The order cannot change the result (only "is any probe blocked" is used, glsl:425).
-__constant__ int c_probe_order[16];
+// Filled by the host with the same FP32 operations.
+__constant__ float c_probe_rv[16];
 
 // ---------------------------------------------------------------- packed f32x2 (FADD2 / FMUL2)
 __device__ __forceinline__ float2 add2(float2 a, float2 b) {
@@ -411,8 +416,6 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
                                                 f3 lightDir, float lightDistance) {
   const int nprobe = light.shadowType == 2 ? 16 : 0;
   const int total = nprobe + (light.pcfSamples > 0 ? light.pcfSamples : 0);
-  const f3 tangent = normalize_ieee(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
-  const f3 bitangent = cross3(lightDir, tangent);
   const float filterSize = light.shadowSoftness * 0.005f;                        // glsl:364 (overwrites :352)
   const float searchSize = light.lightSize * 0.1f;                               // glsl:404
   // t < lightDistance && t < maxRayDistance as one bound; a NaN distance stays NaN (never occluded)
@@ -430,6 +433,8 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
   const Cands cd = scan_candidates(s, cand_base, cone_ok, cone, origin);
   if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
+  const f3 tangent = normalize_ieee(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
+  const f3 bitangent = cross3(lightDir, tangent);
   int unoccluded = 0;
   int j = 0;
   while (j < total) {
@@ -443,7 +448,7 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
       if (idx < end) {
         active |= 1u << r;
         if (probing) {
-          const float rv = halton3(c_probe_order[idx]) * 2.0f - 1.0f;                       // glsl:408
+          const float rv = c_probe_rv[idx];                                                  // glsl:408
           d[r] = normalize_shadow((lightDir + rv * searchSize) + rv * searchSize);           // glsl:409
         } else {
           const int i = idx - nprobe;
@@ -489,17 +494,17 @@ __device__ __noinline__ f3 subsurface(const Scene& s, f3 P, f3 N, const Mat& mat
 
 // Phase barrier of the CTA-coherent mode (see the kernel): keeps the warps that share an SM
 // sub-partition inside the same stretch of code. `coh` is kernel-uniform.
-__device__ __forceinline__ void phase_sync(bool coh) { if (coh) __syncthreads(); }
+__device__ __forceinline__ void phase_sync(bool on) { if (on) __syncthreads(); }
 
 // computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
 // lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
 // Every lane of the CTA walks the light loop (lit = this lane has a surface to shade).
-__device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, bool coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
+__device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, int coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
   f3 Lo = mk3(0.0f, 0.0f, 0.0f);
   const f3 shadow_origin = P + N * 0.001f;               // glsl:381, :412
 #pragma unroll 1
   for (int i = 0; i < s.nl; ++i) {
-    phase_sync(coh);
+    phase_sync(coh >= 3);
     if (!lit) continue;
     const LightRec light = load_light(s, i);
     f3 lightDir = mk3(0.0f, 0.0f, 0.0f);
@@ -542,7 +547,7 @@ struct PixelResult { f3 color, P, N; int object_id; };
 // One invocation of the shader's main() per lane. Whole warps (coh: the whole CTA) call this
 // together; `alive` = this lane still has a path to extend (false from the start for lanes
 // outside the image). The bounce loop ends when no lane of the warp / CTA is alive.
-__device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, saddr cand_base, bool coh,
+__device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, saddr cand_base, int coh,
                                                    bool alive, unsigned px, unsigned py, int frame_count) {
   const rt_frame_params& fp = kp.fp;
   const float noise_r = fetch_noise(tx, (float)(px + (unsigned)frame_count) * fp.noise_scale[0],
@@ -570,7 +575,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 
 #pragma unroll 1
   for (int depth = 0; depth < fp.max_ray_depth; ++depth) {
-    if (!(coh ? __syncthreads_or(alive) : __any_sync(0xffffffffu, alive))) break;
+    if (!(coh >= 2 ? __syncthreads_or(alive) : __any_sync(0xffffffffu, alive))) break;
     bool lit = false;
     f3 N = mk3(0.0f, 0.0f, 0.0f), P = N, V = N;
     Mat mat = {};
@@ -630,7 +635,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 #ifndef RT_PK_MINBLOCKS
 #define RT_PK_MINBLOCKS 2
 #endif
-__global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
+__global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const DeviceScene& sc = kp.sc;
   const rt_frame_params& fp = kp.fp;
@@ -669,7 +674,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(co
   //    no_instruction), tile-level coherence alone gave +52 % throughput.
   //  * independent (large scenes): every warp pulls its own tiles from the global counter; the
   //    object loops are long, cheap sky tiles and expensive reflective tiles balance dynamically.
-  const bool coh = sc.pk_coherent != 0;
+  const int coh = sc.pk_coherent;   // 0 independent warps; 1 CTA blocks; 2 + barrier per bounce; 3 + barrier per light
   __shared__ unsigned s_tile;
   unsigned tile = 0, next = 0;
   if (!coh) {
@@ -685,7 +690,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(co
       if (blk >= kp.blocks_x * kp.blocks_y) break;
       const unsigned by = blk / kp.blocks_x, bx = blk - by * kp.blocks_x;
       const unsigned w = threadIdx.x >> 5;
-      const unsigned tyi = by * 2u + (w >> 2), txi = bx * 4u + (w & 3u);
+      const unsigned tyi = by * (unsigned)kBlockTilesY + (w >> 2), txi = bx * (unsigned)kBlockTilesX + (w & 3u);
       tile = (tyi < kp.tiles_y && txi < kp.tiles_x) ? tyi * kp.tiles_x + txi : num_tiles;
     } else {
       if (tile >= num_tiles) break;
@@ -709,7 +714,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(co
         if (fp.flags & RT_FLAG_ACCUMULATE) {             // partial sums for sample-range sharding
           const float4 old = kp.color[at];
           c = make_float4(old.x + c.x, old.y + c.y, old.z + c.z, 1.0f);
-        } else if (nsamp > 1) {
+        } else if (nsamp > 1 && !(fp.flags & RT_FLAG_SUM_SAMPLES)) {
           c = make_float4(c.x * inv_ns, c.y * inv_ns, c.z * inv_ns, 1.0f);
         }
         kp.color[at] = c;
@@ -725,8 +730,10 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS) rt_packet_kernel(co
   }
 }
 
-inline cudaError_t upload_probe_order(const int* order16) {
-  return cudaMemcpyToSymbol(c_probe_order, order16, sizeof(int) * 16);
+inline cudaError_t upload_probe_order(const float* halton3, const int* order16) {
+  float rv[16];
+  for (int i = 0; i < 16; ++i) rv[i] = halton3[order16[i]] * 2.0f - 1.0f;      // host TU: -ffp-contract=off
+  return cudaMemcpyToSymbol(c_probe_rv, rv, sizeof(rv));
 }
 
 inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
