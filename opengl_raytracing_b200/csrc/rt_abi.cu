@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <utility>
 #include <string>
 #include <vector>
 #include <cuda_fp16.h>
@@ -29,7 +31,7 @@ struct rt_context {
   int n_obj = 0, n_planes = 0, n_lights = 0;
   size_t off_plane = 0, off_material = 0, off_lights = 0;   // in float4 units
   // packet-kernel blob (appended to the same device buffer)
-  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0;
+  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0, pk_clusters = 0;
   // textures
   uint2* d_sky = nullptr; cudaArray_t sky_array = nullptr; cudaTextureObject_t sky_tex = 0; int sky_size = 0;
   unsigned char* d_noise = nullptr; int noise_w = 0, noise_h = 0;
@@ -115,16 +117,30 @@ void stage_scene(const rt_object* obj, int n, const rt_light* lights, int m, int
 // Object[]/Light[] -> the packet kernel's shared-memory image (layout in rt_packet.cuh).
 // Returns the size in float4 units, or 0 when the scene cannot use the sign-select loops
 // (a non-finite bound). `out` may be null to size only.
-struct PkLayout { size_t float4s; int spheres, planes, lights_offset; };
+struct PkLayout { size_t float4s; int spheres, planes, lights_offset, clusters; };
+
+inline unsigned morton10(unsigned v) {                   // spread 10 bits to every third position
+  v &= 1023u;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+
 PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights, int m, float4* out) {
-  PkLayout L = {0, 0, 0, 0};
+  PkLayout L = {0, 0, 0, 0, 0};
   for (int i = 0; i < n; ++i) {
     if (obj[i].type == 0) L.spheres++; else if (obj[i].type == 1) L.planes++;
     if (obj[i].type == 0 || obj[i].type == 1)
       for (int k = 0; k < 3; ++k)
-        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0};
+        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0, 0};
   }
-  size_t bytes = (size_t)L.spheres * 64 + (size_t)L.planes * 128 + (size_t)L.spheres * 4;
+  // Sphere clusters (rt_packet.cuh "two-level boxes"): from kPkClusterMinSpheres spheres on, the
+  // sphere slots are ordered along a Morton curve of their centres and every kPkClusterSize
+  // consecutive slots get a cluster record (union box + bounding sphere).
+  L.clusters = L.spheres >= rt::kPkClusterMinSpheres ? (L.spheres + rt::kPkClusterSize - 1) / rt::kPkClusterSize : 0;
+  size_t bytes = (size_t)L.clusters * 64 + (size_t)L.spheres * 64 + (size_t)L.planes * 128 + (size_t)L.spheres * 4;
   bytes = (bytes + 15) / 16 * 16;
   L.lights_offset = (int)bytes;
   bytes += (size_t)m * sizeof(rt_light);
@@ -133,10 +149,10 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
   if (!out) return L;
   std::memset(out, 0, L.float4s * 16);
   char* base = (char*)out;
-  float* sph = (float*)base;
-  float* pln = (float*)(base + (size_t)L.spheres * 64);
-  int* sph_index = (int*)(base + (size_t)L.spheres * 64 + (size_t)L.planes * 128);
-  int ks = 0, kp = 0;
+  float* clu = (float*)base;
+  float* sph = (float*)(base + (size_t)L.clusters * 64);
+  float* pln = sph + (size_t)L.spheres * 16;
+  int* sph_index = (int*)(pln + (size_t)L.planes * 32);
   auto box = [](float* r, const rt_aabb& b) {          // per axis (lo,hi,hi,lo), lo <= hi
     for (int k = 0; k < 3; ++k) {
       const float lo = b.max[k] < b.min[k] ? b.max[k] : b.min[k];
@@ -144,30 +160,79 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
       r[4 * k + 0] = lo; r[4 * k + 1] = hi; r[4 * k + 2] = hi; r[4 * k + 3] = lo;
     }
   };
+  // slot order of the spheres: array order, or Morton order of the centres when clustered
+  std::vector<int> order;
+  order.reserve(L.spheres);
+  for (int i = 0; i < n; ++i) if (obj[i].type == 0) order.push_back(i);
+  if (L.clusters) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i : order) for (int k = 0; k < 3; ++k) {
+      const float v = obj[i].position[k];
+      if (v < lo[k]) lo[k] = v;
+      if (v > hi[k]) hi[k] = v;
+    }
+    std::vector<std::pair<unsigned, int>> keyed;
+    keyed.reserve(order.size());
+    for (int i : order) {
+      unsigned code = 0;
+      for (int k = 0; k < 3; ++k) {
+        const float ext = hi[k] - lo[k];
+        float q = ext > 0.f ? (obj[i].position[k] - lo[k]) / ext * 1023.f : 0.f;
+        if (!(q >= 0.f)) q = 0.f;                      // NaN centres sort first
+        if (q > 1023.f) q = 1023.f;
+        code |= morton10((unsigned)q) << k;
+      }
+      keyed.emplace_back(code, i);
+    }
+    std::sort(keyed.begin(), keyed.end());
+    for (size_t j = 0; j < keyed.size(); ++j) order[j] = keyed[j].second;
+  }
+  for (int ks = 0; ks < L.spheres; ++ks) {
+    const rt_object& o = obj[order[ks]];
+    float* r = sph + (size_t)ks * 16;
+    box(r, o.bounds);
+    r[12] = o.position[0]; r[13] = o.position[1]; r[14] = o.position[2]; r[15] = o.radius;
+    sph_index[ks] = order[ks];
+  }
+  for (int c = 0; c < L.clusters; ++c) {
+    const int first = c * rt::kPkClusterSize, last = std::min(L.spheres, first + rt::kPkClusterSize);
+    float* r = clu + (size_t)c * 16;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int ks = first; ks < last; ++ks) for (int k = 0; k < 3; ++k) {
+      const float* mr = sph + (size_t)ks * 16 + 4 * k;   // member (lo,hi,...)
+      if (mr[0] < lo[k]) lo[k] = mr[0];
+      if (mr[1] > hi[k]) hi[k] = mr[1];
+    }
+    for (int k = 0; k < 3; ++k) { r[4 * k + 0] = lo[k]; r[4 * k + 1] = hi[k]; r[4 * k + 2] = hi[k]; r[4 * k + 3] = lo[k]; }
+    // bounding sphere of the member spheres (double precision, then inflated) for the cone test
+    double cx = 0.5 * ((double)lo[0] + hi[0]), cy = 0.5 * ((double)lo[1] + hi[1]), cz = 0.5 * ((double)lo[2] + hi[2]), R = 0.0;
+    for (int ks = first; ks < last; ++ks) {
+      const float* mr = sph + (size_t)ks * 16;
+      const double dx = mr[12] - cx, dy = mr[13] - cy, dz = mr[14] - cz;
+      const double d = std::sqrt(dx * dx + dy * dy + dz * dz) + std::fabs((double)mr[15]);
+      if (!(d <= R)) R = d;                              // NaN radius/centre -> NaN bound -> never culled
+    }
+    r[12] = (float)cx; r[13] = (float)cy; r[14] = (float)cz; r[15] = (float)(R * 1.001 + 1e-6);
+  }
+  int kp = 0;
   for (int i = 0; i < n; ++i) {
     const rt_object& o = obj[i];
-    if (o.type == 0) {
-      float* r = sph + (size_t)ks * 16;
-      box(r, o.bounds);
-      r[12] = o.position[0]; r[13] = o.position[1]; r[14] = o.position[2]; r[15] = o.radius;
-      sph_index[ks++] = i;
-    } else if (o.type == 1) {
-      float* r = pln + (size_t)kp * 32;
-      box(r, o.bounds);
-      const h3 nrm = {o.normal[0], o.normal[1], o.normal[2]};
-      h3 right, forward;                               // frame of glsl:130-138, hoisted per object
-      if (std::fabs(nrm.y) > 0.9f) right = hnormalize(hcross(nrm, h3{0.f, 0.f, 1.f}));
-      else right = hnormalize(hcross(nrm, h3{0.f, 1.f, 0.f}));
-      forward = hnormalize(hcross(right, nrm));
-      r[12] = nrm.x; r[13] = nrm.y; r[14] = nrm.z; r[15] = o.size[0] / 2.0f;
-      r[16] = right.x; r[17] = right.y; r[18] = right.z; r[19] = o.size[1] / 2.0f;
-      r[20] = forward.x; r[21] = forward.y; r[22] = forward.z; r[23] = 0.f;
-      r[24] = o.position[0]; r[25] = o.position[1]; r[26] = o.position[2];
-      std::memcpy(&r[27], &i, 4);
-      // conservative bounds for the shadow-job cone test: rectangle bounding radius, |normal|
-      r[28] = std::sqrt(r[15] * r[15] + r[19] * r[19]) * 1.0001f; r[29] = std::sqrt(hdot(nrm, nrm)) * 1.0001f;
-      kp++;
-    }
+    if (o.type != 1) continue;
+    float* r = pln + (size_t)kp * 32;
+    box(r, o.bounds);
+    const h3 nrm = {o.normal[0], o.normal[1], o.normal[2]};
+    h3 right, forward;                               // frame of glsl:130-138, hoisted per object
+    if (std::fabs(nrm.y) > 0.9f) right = hnormalize(hcross(nrm, h3{0.f, 0.f, 1.f}));
+    else right = hnormalize(hcross(nrm, h3{0.f, 1.f, 0.f}));
+    forward = hnormalize(hcross(right, nrm));
+    r[12] = nrm.x; r[13] = nrm.y; r[14] = nrm.z; r[15] = o.size[0] / 2.0f;
+    r[16] = right.x; r[17] = right.y; r[18] = right.z; r[19] = o.size[1] / 2.0f;
+    r[20] = forward.x; r[21] = forward.y; r[22] = forward.z; r[23] = 0.f;
+    r[24] = o.position[0]; r[25] = o.position[1]; r[26] = o.position[2];
+    std::memcpy(&r[27], &i, 4);
+    // conservative bounds for the shadow-job cone test: rectangle bounding radius, |normal|
+    r[28] = std::sqrt(r[15] * r[15] + r[19] * r[19]) * 1.0001f; r[29] = std::sqrt(hdot(nrm, nrm)) * 1.0001f;
+    kp++;
   }
   if (m > 0) std::memcpy(base + L.lights_offset, lights, (size_t)m * sizeof(rt_light));
   return L;
@@ -290,7 +355,7 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
   c->n_obj = n; c->n_planes = planes; c->n_lights = m;
   c->off_plane = off_plane; c->off_material = off_material; c->off_lights = off_lights;
   c->off_pk = off_pk; c->pk_float4s = pkl.float4s; c->pk_spheres = pkl.spheres; c->pk_planes = pkl.planes;
-  c->pk_lights_offset = pkl.lights_offset;
+  c->pk_lights_offset = pkl.lights_offset; c->pk_clusters = pkl.clusters;
   if (async) {
     RT_CUDA(c, cudaEventRecord(c->stage_done, stream));
     c->stage_pending = true;
@@ -400,9 +465,11 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
                           c->pk_float4s * sizeof(float4) + 24 * 1024 * 2 <= (size_t)c->max_smem_optin - 1024;
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
+  sc.pk_num_clusters = c->pk_clusters;
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);
   // with long loops the barrier imbalance costs more than the fetch locality gains.
-  sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : (c->pk_spheres + c->pk_planes <= 48 ? 3 : 0);
+  sc.pk_big = c->pk_spheres + c->pk_planes > 48 ? 1 : 0;
+  sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : 3;   // small-scene kernel only
   unsigned warps = 0;
   const bool par = (p->flags & RT_FLAG_PARITY_MATH) != 0u;
   cudaError_t e;

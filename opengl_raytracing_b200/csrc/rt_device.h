@@ -7,6 +7,11 @@
 
 namespace rt {
 
+// Packet-kernel sphere clusters: every kPkClusterSize consecutive sphere slots share one
+// cluster record; built from kPkClusterMinSpheres spheres on (rt_abi.cu stage_scene_packet).
+constexpr int kPkClusterSize = 16;
+constexpr int kPkClusterMinSpheres = 64;
+
 // Device-resident scene in the layout the kernel stages into shared memory. Built on the
 // host by stage_scene() from the std430 Object[]/Light[] bytes (rt_upload_scene); every
 // derived value is computed with the same FP32 operations the shader would use per call,
@@ -36,13 +41,15 @@ struct DeviceScene {
   int sky_size;
   const unsigned char* noise;  // R8
   int noise_w, noise_h;
-  // packet-kernel scene blob (rt_packet.cuh): sphere records (64 B), plane records (128 B),
+  // packet-kernel scene blob (rt_packet.cuh): cluster records (64 B), sphere records (64 B), plane records (128 B),
   // sphere_index (4 B each), padding to 16 B, raw light records (96 B). Copied verbatim into
   // shared memory by every CTA. pk_float4s == 0: the packet kernel cannot take this scene.
   const float4* pk_blob;
   int pk_float4s;
   int pk_num_spheres, pk_num_planes;
+  int pk_num_clusters;       // 0: no cluster level (fewer than kPkClusterMinSpheres spheres)
   int pk_lights_offset;      // bytes from the start of the blob
+  int pk_big;                // 1: large-scene kernel (independent warps, two-level boxes)
   int pk_coherent;           // 1: CTA-coherent phases (small scenes), 0: independent warps
 };
 

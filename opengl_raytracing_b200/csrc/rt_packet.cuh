@@ -76,17 +76,21 @@ __device__ __forceinline__ f3 normalize_shadow(f3 a) { return a * rsqrtf(dot3(a,
 //                         (forward.xyz, 0) (position.xyz, original index bits)
 //                         (bounding radius of the rectangle, |normal|, 0, 0)
 //   sphere_index   4 B  : original object index of each sphere slot
+//   cluster record 64 B : (lo,hi,hi,lo) x3 of the union of the boxes of sphere slots [16c, 16c+16),
+//                         (centre, radius) of a sphere containing those spheres. Present from 64
+//                         spheres on; the slots are then in Morton order of the centres.
 // lo/hi are sorted per axis on the host (the shader's min/max make the test symmetric in them).
 constexpr int kSphereBytes = 64, kPlaneBytes = 128;
 
 typedef unsigned saddr;        // 32-bit shared-window address: explicit LDS, one register
 struct Scene {
+  saddr clu;                  // shared memory: nc cluster records (union box + bounding sphere), may be empty
   saddr sph;                  // shared memory
   saddr pln;                  // shared memory
   saddr sph_index;            // shared memory
   saddr lights;               // shared memory, raw 96-B records
   const float4* material;     // global memory, 4 float4 per ORIGINAL object index
-  int ns, np, nl;
+  int nc, ns, np, nl;
   float maxd;
 };
 
@@ -153,20 +157,35 @@ __device__ __forceinline__ int hit_object_index(const Scene& s, int code) {
   return code < s.ns ? lds32i(s.sph_index + 4u * (unsigned)code) : lds32i(s.pln + (unsigned)(code - s.ns) * kPlaneBytes + 108u);
 }
 
-// Closest hit of one ray over the whole scene, the shader's tie rule (glsl:155-196).
-// GENERIC: explicit min/max per axis (any direction, incl. NaN and 0).
-template <bool GENERIC>
-__device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, float a) {
-  // per-axis running addresses of the (near,far) pair this ray's sign selects
-  saddr ax = s.sph + ((!GENERIC && d.x < 0.0f) ? 8u : 0u);
-  saddr ay = s.sph + ((!GENERIC && d.y < 0.0f) ? 24u : 16u);
-  saddr az = s.sph + ((!GENERIC && d.z < 0.0f) ? 40u : 32u);
+constexpr int kCandCap = 24;          // per-thread scratch list (u16 codes) in shared memory
+__device__ __forceinline__ void cand_store(saddr cand_base, int i, int code) {
+  asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)i * (kThreads * 2u)), "h"((unsigned short)code) : "memory");
+}
+__device__ __forceinline__ int cand_load(saddr cand_base, int i) {
+  unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(cand_base + (unsigned)i * (kThreads * 2u)) : "memory");
+  return (int)v;
+}
+
+// Closest hit of one ray over the whole scene, the shader's tie rule (glsl:155-196): among equal
+// t the lower ORIGINAL index wins (what the in-order strict `<` of :178 does), so the visiting
+// order is free. GENERIC: explicit min/max per axis (any direction, incl. NaN and 0), no clusters.
+//
+// Two-level boxes: with clusters, the ray first runs the SAME slab arithmetic against the union
+// box of each 16 sphere slots. IEEE rounding is monotone, so (lo_u - o)*inv <= (lo_m - o)*inv for
+// every member box m of the union u (and >= for hi): a ray that fails the union box fails every
+// member box — the cluster test is exactly conservative, no tolerance involved. Passing clusters
+// go to the lane's scratch list, then each lane walks the members of its own clusters.
+template <bool GENERIC, bool BIG>
+__device__ __forceinline__ Hit trace_one(const Scene& s, saddr cand_base, f3 o, f3 d, f3 inv, float a) {
+  const unsigned offx = (!GENERIC && d.x < 0.0f) ? 8u : 0u;      // the (near,far) pair this ray's sign selects
+  const unsigned offy = (!GENERIC && d.y < 0.0f) ? 24u : 16u;
+  const unsigned offz = (!GENERIC && d.z < 0.0f) ? 40u : 32u;
   const float nox = -o.x, noy = -o.y, noz = -o.z;
   Hit h; h.code = -1; h.t = s.maxd;
-  auto slab = [&](unsigned off) -> bool {
-    const float2 X = mul2(add2(lds64(ax + off), dup2(nox)), dup2(inv.x));
-    const float2 Y = mul2(add2(lds64(ay + off), dup2(noy)), dup2(inv.y));
-    const float2 Z = mul2(add2(lds64(az + off), dup2(noz)), dup2(inv.z));
+  auto slab = [&](saddr ax, saddr ay, saddr az) -> bool {
+    const float2 X = mul2(add2(lds64(ax), dup2(nox)), dup2(inv.x));
+    const float2 Y = mul2(add2(lds64(ay), dup2(noy)), dup2(inv.y));
+    const float2 Z = mul2(add2(lds64(az), dup2(noz)), dup2(inv.z));
     float tmin, tmax;
     if (GENERIC) {
       tmin = fmax3(fminf(X.x, X.y), fminf(Y.x, Y.y), fminf(Z.x, Z.y));
@@ -179,24 +198,50 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, flo
   };
   auto sphere = [&](int k) {
     float t;
-    if (sphere_t(lds128(s.sph + (unsigned)k * kSphereBytes + 48u), o, d, a, t) && t < h.t) {   // t > 0 checked in sphere_t
+    if (!sphere_t(lds128(s.sph + (unsigned)k * kSphereBytes + 48u), o, d, a, t)) return;   // t > 0 checked in sphere_t
+    if (t < h.t || (t == h.t && h.code >= 0 && hit_object_index(s, k) < hit_object_index(s, h.code))) {
       h.code = k; h.t = t;
     }
   };
-  int k = 0;
-  for (; k + 2 <= s.ns; k += 2, ax += 2 * kSphereBytes, ay += 2 * kSphereBytes, az += 2 * kSphereBytes) {
-    const bool p0 = slab(0u), p1 = slab((unsigned)kSphereBytes);
-    if (p0 | p1) {
-      if (p0) sphere(k);
-      if (p1) sphere(k + 1);
+  bool linear = true;
+  if (BIG && !GENERIC && s.nc > 0) {
+    int n = 0;
+    saddr ax = s.clu + offx, ay = s.clu + offy, az = s.clu + offz;
+#pragma unroll 2
+    for (int c = 0; c < s.nc; ++c, ax += kSphereBytes, ay += kSphereBytes, az += kSphereBytes) {
+      if (!slab(ax, ay, az)) continue;
+      if (n < kCandCap) cand_store(cand_base, n, c);
+      ++n;
+    }
+    if (n <= kCandCap) {
+      linear = false;
+#pragma unroll 1
+      for (int i = 0; i < n; ++i) {
+        const int first = cand_load(cand_base, i) * kPkClusterSize;
+        const int last = min(first + kPkClusterSize, s.ns);
+        const saddr rec = s.sph + (unsigned)first * kSphereBytes;
+        ax = rec + offx; ay = rec + offy; az = rec + offz;
+#pragma unroll 2
+        for (int k = first; k < last; ++k, ax += kSphereBytes, ay += kSphereBytes, az += kSphereBytes)
+          if (slab(ax, ay, az)) sphere(k);
+      }
     }
   }
-  if (k < s.ns && slab(0u)) sphere(k);
-  const unsigned tail = (unsigned)(s.ns - k) * kSphereBytes;   // s.pln follows the sphere records
-  ax += tail; ay += tail; az += tail;
+  if (linear) {
+    saddr ax = s.sph + offx, ay = s.sph + offy, az = s.sph + offz;
+    int k = 0;
+    for (; k + 2 <= s.ns; k += 2, ax += 2 * kSphereBytes, ay += 2 * kSphereBytes, az += 2 * kSphereBytes) {
+      const bool p0 = slab(ax, ay, az), p1 = slab(ax + kSphereBytes, ay + kSphereBytes, az + kSphereBytes);
+      if (p0 | p1) {
+        if (p0) sphere(k);
+        if (p1) sphere(k + 1);
+      }
+    }
+    if (k < s.ns && slab(ax, ay, az)) sphere(k);
+  }
   saddr rec = s.pln;
-  for (int j = 0; j < s.np; ++j, rec += kPlaneBytes, ax += kPlaneBytes, ay += kPlaneBytes, az += kPlaneBytes) {
-    if (!slab(0u)) continue;
+  for (int j = 0; j < s.np; ++j, rec += kPlaneBytes) {
+    if (!slab(rec + offx, rec + offy, rec + offz)) continue;
     float t;
     if (!plane_t(rec, o, d, t) || !(t > 0.0f)) continue;
     if (t < h.t || (t == h.t && h.code >= 0 && lds32i(rec + 108u) < hit_object_index(s, h.code))) {
@@ -208,16 +253,17 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, f3 o, f3 d, f3 inv, flo
 
 // The cold variant lives behind a call so the hot loop stays small in the instruction cache.
 __device__ __noinline__ Hit trace_closest_generic(const Scene& s, f3 o, f3 d, f3 inv, float a) {
-  return trace_one<true>(s, o, d, inv, a);
+  return trace_one<true, false>(s, 0u, o, d, inv, a);
 }
 
 // Closest hit for primary / bounce / SSS rays. IEEE 1/dir in both builds: the hit set of these
 // rays feeds P and N.
-__device__ __forceinline__ Hit trace_closest(const Scene& s, f3 o, f3 d) {
+template <bool BIG>
+__device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3 o, f3 d) {
   const f3 inv = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
   const float a = dot3(d, d);
   if (!dir_regular(d, a)) return trace_closest_generic(s, o, d, inv, a);
-  return trace_one<false>(s, o, d, inv, a);
+  return trace_one<false, BIG>(s, cand_base, o, d, inv, a);
 }
 
 // ---------------------------------------------------------------- shadow jobs: cone culling
@@ -232,8 +278,6 @@ __device__ __forceinline__ Hit trace_closest(const Scene& s, f3 o, f3 d) {
 // Conservative: sin is over-, cos under-estimated, radii are inflated by 1e-3, and the squared
 // comparison carries a 4e-6*|v|^2 slack (40x the rounding of d2 - along^2, and above the
 // 1e-7*|v|^2 by which the shader's own discriminant can report a grazing hit).
-constexpr int kCandCap = 24;          // per-thread candidate list (u16 codes) in shared memory
-
 struct Cone { f3 L; float s, c2, far; };        // axis, sin bound, cos^2 bound, far = lim*(1+e)
 struct Cands { saddr base; int n; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test)
 
@@ -261,28 +305,44 @@ __device__ __forceinline__ bool cone_misses_plane(const Cone& c, f3 o, saddr rec
 __device__ __forceinline__ saddr record_of(const Scene& s, int code) {
   return code < s.ns ? s.sph + (unsigned)code * kSphereBytes : s.pln + (unsigned)(code - s.ns) * kPlaneBytes;
 }
-__device__ __forceinline__ int cand_code(const Cands& cd, int i) {
-  if (!cd.list) return i;
-  unsigned short v; asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(cd.base + (unsigned)i * (kThreads * 2u)));
-  return (int)v;
-}
+__device__ __forceinline__ int cand_code(const Cands& cd, int i) { return cd.list ? cand_load(cd.base, i) : i; }
 
 // One scan of the scene per shadow job. Returns the candidate set for the job's packets.
+template <bool BIG>
 __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base, bool cone_ok, const Cone& cone, f3 o) {
   Cands cd; cd.base = cand_base; cd.n = s.ns + s.np; cd.list = false; cd.prefilter = false;
   if (!cone_ok) return cd;
   int n = 0;
-  saddr rec = s.sph;
+  if (BIG && s.nc > 0) {                                     // cluster bounding spheres first, then members
+    saddr crec = s.clu;
+#pragma unroll 1
+    for (int c = 0; c < s.nc; ++c, crec += kSphereBytes) {
+      const float4 cs = lds128(crec + 48u);
+      if (cone_misses_sphere(cone, o, xyz(cs), cs.w)) continue;
+      const int first = c * kPkClusterSize, last = min(first + kPkClusterSize, s.ns);
+      saddr rec = s.sph + (unsigned)first * kSphereBytes;
 #pragma unroll 2
-  for (int k = 0; k < s.ns; ++k, rec += kSphereBytes) {
-    const float4 sp = lds128(rec + 48u);
-    if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
-    if (n < kCandCap) asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)n * (kThreads * 2u)), "h"((unsigned short)k) : "memory");
-    ++n;
+      for (int k = first; k < last; ++k, rec += kSphereBytes) {
+        const float4 sp = lds128(rec + 48u);
+        if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
+        if (n < kCandCap) cand_store(cand_base, n, k);
+        ++n;
+      }
+    }
+  } else {
+    saddr rec = s.sph;
+#pragma unroll 2
+    for (int k = 0; k < s.ns; ++k, rec += kSphereBytes) {
+      const float4 sp = lds128(rec + 48u);
+      if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
+      if (n < kCandCap) cand_store(cand_base, n, k);
+      ++n;
+    }
   }
+  saddr rec = s.pln;
   for (int j = 0; j < s.np; ++j, rec += kPlaneBytes) {
     if (cone_misses_plane(cone, o, rec)) continue;
-    if (n < kCandCap) asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)n * (kThreads * 2u)), "h"((unsigned short)(s.ns + j)) : "memory");
+    if (n < kCandCap) cand_store(cand_base, n, s.ns + j);
     ++n;
   }
   if (n <= kCandCap) { cd.list = true; cd.n = n; }
@@ -412,6 +472,7 @@ __device__ __forceinline__ Mat load_material(const Scene& s, int index) {
 // calculateShadow (glsl:442-455) for shadowType 1 (pcfShadow, glsl:342-397) and 2 (pcssShadow,
 // glsl:400-440 = "fully lit unless one of 16 fixed probes is blocked, else PCF"). Probes and PCF
 // samples run through ONE packet site: jobs [0,nprobe) are probes, [nprobe,nprobe+pcf) samples.
+template <bool BIG>
 __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
                                                 f3 lightDir, float lightDistance) {
   const int nprobe = light.shadowType == 2 ? 16 : 0;
@@ -431,7 +492,7 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   cone.far = fmaxf(lim_pcf, lim_probe) * (1.0f + cone.s) * 1.0001f;              // NaN limits: fmaxf keeps the other
   const float ll = dot3(lightDir, lightDir);
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
-  const Cands cd = scan_candidates(s, cand_base, cone_ok, cone, origin);
+  const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin);
   if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
   const f3 tangent = normalize_ieee(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
   const f3 bitangent = cross3(lightDir, tangent);
@@ -499,6 +560,7 @@ __device__ __forceinline__ void phase_sync(bool on) { if (on) __syncthreads(); }
 // computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
 // lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
 // Every lane of the CTA walks the light loop (lit = this lane has a surface to shade).
+template <bool BIG>
 __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, int coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
   f3 Lo = mk3(0.0f, 0.0f, 0.0f);
   const f3 shadow_origin = P + N * 0.001f;               // glsl:381, :412
@@ -534,7 +596,7 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     if (brdf.x == 0.0f && brdf.y == 0.0f && brdf.z == 0.0f && (!sampled || light.pcfSamples > 0)) continue;
     float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
     if (light.shadowType == 0) shadowFactor = 1.0f;
-    else if (sampled) shadowFactor = shadow_packets(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
+    else if (sampled) shadowFactor = shadow_packets<BIG>(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
     Lo = Lo + brdf * shadowFactor;
   }
   if (lit && mat.subsurfaceScatter > 0.0f) Lo = Lo + subsurface(s, P, N, mat);
@@ -547,6 +609,7 @@ struct PixelResult { f3 color, P, N; int object_id; };
 // One invocation of the shader's main() per lane. Whole warps (coh: the whole CTA) call this
 // together; `alive` = this lane still has a path to extend (false from the start for lanes
 // outside the image). The bounce loop ends when no lane of the warp / CTA is alive.
+template <bool BIG>
 __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, saddr cand_base, int coh,
                                                    bool alive, unsigned px, unsigned py, int frame_count) {
   const rt_frame_params& fp = kp.fp;
@@ -580,7 +643,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
     f3 N = mk3(0.0f, 0.0f, 0.0f), P = N, V = N;
     Mat mat = {};
     if (alive) {
-      const Hit h = trace_closest(s, ro, rd);
+      const Hit h = trace_closest<BIG>(s, cand_base, ro, rd);
       if (h.code < 0) {                         // miss path (glsl:530-534)
         const f3 sky = fp.use_skybox ? fetch_sky(tx, rd) : mk3(0.0f, 0.0f, 0.0f);
         out.color = out.color + throughput * sky;
@@ -596,7 +659,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
         out.P = P; out.N = N; out.object_id = index;
       }
     }
-    const f3 Lo = compute_lighting(s, cand_base, coh, lit, noise_r, P, N, mat, V);
+    const f3 Lo = compute_lighting<BIG>(s, cand_base, coh, lit, noise_r, P, N, mat, V);
     if (!lit) continue;
     out.color = out.color + throughput * Lo;
 
@@ -635,6 +698,10 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 #ifndef RT_PK_MINBLOCKS
 #define RT_PK_MINBLOCKS 2
 #endif
+// BIG = false: small scenes (CTA-coherent phases, no cluster code in the instruction stream);
+// BIG = true: large scenes (independent warps, two-level boxes). One source, two compact kernels:
+// on C2 every extra KB of hot code costs (measured +9 % when the cluster loops were compiled in).
+template <bool BIG>
 __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const DeviceScene& sc = kp.sc;
@@ -645,12 +712,13 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) r
   __syncthreads();
   Scene s;
   const saddr base = (saddr)__cvta_generic_to_shared(smem);
-  s.sph = base;
-  s.pln = base + (unsigned)sc.pk_num_spheres * kSphereBytes;
+  s.clu = base;
+  s.sph = base + (unsigned)sc.pk_num_clusters * kSphereBytes;
+  s.pln = s.sph + (unsigned)sc.pk_num_spheres * kSphereBytes;
   s.sph_index = s.pln + (unsigned)sc.pk_num_planes * kPlaneBytes;
   s.lights = base + (unsigned)sc.pk_lights_offset;
   s.material = sc.material;
-  s.ns = sc.pk_num_spheres; s.np = sc.pk_num_planes; s.nl = sc.num_lights;
+  s.nc = BIG ? sc.pk_num_clusters : 0; s.ns = sc.pk_num_spheres; s.np = sc.pk_num_planes; s.nl = sc.num_lights;
   s.maxd = fp.max_ray_distance;
   // per-thread candidate list behind the scene image: entry i of thread t at +(i*kThreads + t)*2
   const saddr cand_base = base + (unsigned)sc.pk_float4s * 16u + threadIdx.x * 2u;
@@ -674,7 +742,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) r
   //    no_instruction), tile-level coherence alone gave +52 % throughput.
   //  * independent (large scenes): every warp pulls its own tiles from the global counter; the
   //    object loops are long, cheap sky tiles and expensive reflective tiles balance dynamically.
-  const int coh = sc.pk_coherent;   // 0 independent warps; 1 CTA blocks; 2 + barrier per bounce; 3 + barrier per light
+  const int coh = BIG ? 0 : sc.pk_coherent;   // 0 independent warps; 1 CTA blocks; 2 + barrier per bounce; 3 + barrier per light
   __shared__ unsigned s_tile;
   unsigned tile = 0, next = 0;
   if (!coh) {
@@ -703,7 +771,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) r
     PixelResult r;                                       // position/normal/id: those of sample 0
 #pragma unroll 1
     for (int sidx = 0; sidx < nsamp; ++sidx) {           // colour: sequential FP32 sum over samples
-      const PixelResult r2 = shade_pixel(kp, s, tx, cand_base, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
+      const PixelResult r2 = shade_pixel<BIG>(kp, s, tx, cand_base, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
       if (sidx == 0) r = r2;
       else r.color = r.color + r2.color;
     }
@@ -736,12 +804,13 @@ inline cudaError_t upload_probe_order(const float* halton3, const int* order16) 
   return cudaMemcpyToSymbol(c_probe_rv, rv, sizeof(rv));
 }
 
-inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+template <bool BIG>
+inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
-  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel, kThreads, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel<BIG>, kThreads, smem);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
@@ -752,10 +821,16 @@ inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStrea
   // how far the work counter advances during this launch (reported through *warps_launched
   // as "advance - num_tiles", the form rt_render adds back): independent mode = one fetch per
   // tile + one failing fetch per warp; coherent mode = one per block + one per CTA.
-  if (kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
+  if (!BIG && kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
   else *warps_launched = ctas * kWarpsPerCta;
-  rt_packet_kernel<<<ctas, kThreads, smem, stream>>>(kp);
+  rt_packet_kernel<BIG><<<ctas, kThreads, smem, stream>>>(kp);
   return cudaGetLastError();
+}
+
+// kp.sc.pk_big (host-chosen by object count) selects the kernel.
+inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+  return kp.sc.pk_big ? launch_packet_t<true>(kp, sm_count, stream, warps_launched)
+                      : launch_packet_t<false>(kp, sm_count, stream, warps_launched);
 }
 
 }  // namespace pk
