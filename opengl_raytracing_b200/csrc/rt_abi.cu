@@ -462,7 +462,7 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   // (the packet blob is staged for the full scene), or the scene does not fit shared memory.
   const bool full_scene = p->num_objects == c->n_obj && p->num_lights == c->n_lights;
   const bool use_packet = !(p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) && full_scene && c->pk_float4s > 0 &&
-                          c->pk_float4s * sizeof(float4) + 24 * 1024 * 2 <= (size_t)c->max_smem_optin - 1024;
+                          c->pk_float4s * sizeof(float4) + 32 * 1024 * 2 <= (size_t)c->max_smem_optin - 1024;
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   sc.pk_num_clusters = c->pk_clusters;

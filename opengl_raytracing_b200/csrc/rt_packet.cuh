@@ -157,7 +157,21 @@ __device__ __forceinline__ int hit_object_index(const Scene& s, int code) {
   return code < s.ns ? lds32i(s.sph_index + 4u * (unsigned)code) : lds32i(s.pln + (unsigned)(code - s.ns) * kPlaneBytes + 108u);
 }
 
-constexpr int kCandCap = 24;          // per-thread scratch list (u16 codes) in shared memory
+// Dev-only statistics build (-DRT_PK_STATS=1): per-thread atomics into kp.counters, read with
+// rt_get_counters. 0 jobs, 1 jobs with no candidate, 2 overflow jobs, 3 candidates (list jobs),
+// 4 prescan cone tests, 5 packets traced, 6 packet-loop object visits, 7 closest rays,
+// 8 cluster slab tests, 9 member slab tests, 10 closest linear fallbacks
+#ifndef RT_PK_STATS
+#define RT_PK_STATS 0
+#endif
+#if RT_PK_STATS
+__device__ unsigned long long* g_stats;
+#define PK_STAT(i, n) atomicAdd(g_stats + (i), (unsigned long long)(n))
+#else
+#define PK_STAT(i, n) ((void)0)
+#endif
+
+constexpr int kCandCap = 32;          // per-thread scratch list (u16 codes) in shared memory
 __device__ __forceinline__ void cand_store(saddr cand_base, int i, int code) {
   asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)i * (kThreads * 2u)), "h"((unsigned short)code) : "memory");
 }
@@ -204,8 +218,10 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, saddr cand_base, f3 o, 
     }
   };
   bool linear = true;
+  PK_STAT(7, 1);
   if (BIG && !GENERIC && s.nc > 0) {
     int n = 0;
+    PK_STAT(8, s.nc);
     saddr ax = s.clu + offx, ay = s.clu + offy, az = s.clu + offz;
 #pragma unroll 2
     for (int c = 0; c < s.nc; ++c, ax += kSphereBytes, ay += kSphereBytes, az += kSphereBytes) {
@@ -213,12 +229,14 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, saddr cand_base, f3 o, 
       if (n < kCandCap) cand_store(cand_base, n, c);
       ++n;
     }
+    if (n > kCandCap) PK_STAT(10, 1);
     if (n <= kCandCap) {
       linear = false;
 #pragma unroll 1
       for (int i = 0; i < n; ++i) {
         const int first = cand_load(cand_base, i) * kPkClusterSize;
         const int last = min(first + kPkClusterSize, s.ns);
+        PK_STAT(9, last - first);
         const saddr rec = s.sph + (unsigned)first * kSphereBytes;
         ax = rec + offx; ay = rec + offy; az = rec + offz;
 #pragma unroll 2
@@ -278,18 +296,23 @@ __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3
 // Conservative: sin is over-, cos under-estimated, radii are inflated by 1e-3, and the squared
 // comparison carries a 4e-6*|v|^2 slack (40x the rounding of d2 - along^2, and above the
 // 1e-7*|v|^2 by which the shader's own discriminant can report a grazing hit).
-struct Cone { f3 L; float s, c2, far; };        // axis, sin bound, cos^2 bound, far = lim*(1+e)
+struct Cone { f3 L; float s, c2, far; f3 fn; float fe; };   // axis, sin bound, cos^2 bound, far = lim*(1+e); fan plane normal (0 = none), PCF slack
 struct Cands { saddr base; int n; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test)
 
 __device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 center, float r) {
   const f3 v = center - o;
   const float along = fmaf(v.z, c.L.z, fmaf(v.y, c.L.y, v.x * c.L.x));
   const float d2 = fmaf(v.z, v.z, fmaf(v.y, v.y, v.x * v.x));
-  const float rr = r * 1.001f;
+  const float rr = fabsf(r) * 1.001f;                       // a negative radius is the same sphere (glsl:108 squares it)
   const float q = fmaf(along, c.s, rr);                     // r' + along*sin
   const float lhs = fmaf(-along, along, d2) * c.c2;         // perp^2 * cos^2
   const float rhs = fmaf(d2, 4.0e-6f, q * q);
-  return q < 0.0f || lhs > rhs || along - rr > c.far;      // any NaN: not culled
+  if (q < 0.0f || lhs > rhs || along - rr > c.far) return true;      // any NaN: not culled
+  // PCSS fan: the 16 probes all lie in the plane through o spanned by L and (1,1,1) (glsl:409 adds
+  // the same scalar to x, y and z), the PCF samples within fe of L: a sphere farther than that from
+  // the plane is out of reach. fn = 0 (no probes, or L || (1,1,1)) disables the test.
+  const float w = fmaf(v.z, c.fn.z, fmaf(v.y, c.fn.y, v.x * c.fn.x));
+  return fabsf(w) > fmaf(sqrtf(d2) * 1.001f + rr, c.fe, rr);
 }
 __device__ __forceinline__ bool cone_misses_plane(const Cone& c, f3 o, saddr rec) {
   const float4 pn = lds128(rec + 48u), pp = lds128(rec + 96u), pb = lds128(rec + 112u);
@@ -318,7 +341,9 @@ __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base
 #pragma unroll 1
     for (int c = 0; c < s.nc; ++c, crec += kSphereBytes) {
       const float4 cs = lds128(crec + 48u);
+      PK_STAT(4, 1);
       if (cone_misses_sphere(cone, o, xyz(cs), cs.w)) continue;
+      PK_STAT(4, min(kPkClusterSize, s.ns - c * kPkClusterSize));
       const int first = c * kPkClusterSize, last = min(first + kPkClusterSize, s.ns);
       saddr rec = s.sph + (unsigned)first * kSphereBytes;
 #pragma unroll 2
@@ -345,8 +370,10 @@ __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base
     if (n < kCandCap) cand_store(cand_base, n, s.ns + j);
     ++n;
   }
-  if (n <= kCandCap) { cd.list = true; cd.n = n; }
-  else cd.prefilter = true;                                  // too many survivors: full scan, cone test inline
+  PK_STAT(0, 1);
+  if (n == 0) PK_STAT(1, 1);
+  if (n <= kCandCap) { cd.list = true; cd.n = n; PK_STAT(3, n); }
+  else { cd.prefilter = true; PK_STAT(2, 1); }                                  // too many survivors: full scan, cone test inline
   return cd;
 }
 
@@ -400,6 +427,7 @@ __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands
     }
   }
   const float nox = -o.x, noy = -o.y, noz = -o.z;
+  PK_STAT(5, 1);
 #pragma unroll 1
   while (remaining) {
     const unsigned lead = (signs >> (3 * (__ffs(remaining) - 1))) & 7u;
@@ -412,6 +440,7 @@ __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands
 #pragma unroll 1
     for (int i = 0; i < cd.n; ++i) {
       const int code = cand_code(cd, i);
+      PK_STAT(6, 1);
       const saddr rec = record_of(s, code);
       const bool is_sphere = code < s.ns;
       if (cd.prefilter && (is_sphere ? cone_misses_sphere(cone, o, xyz(lds128(rec + 48u)), lds32(rec + 60u)) : cone_misses_plane(cone, o, rec))) continue;
@@ -490,6 +519,13 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   cone.s = fmaxf(e_pcf, e_probe) * 1.01f + 1.0e-5f;
   cone.c2 = (1.0f - cone.s * cone.s) * 0.999f;
   cone.far = fmaxf(lim_pcf, lim_probe) * (1.0f + cone.s) * 1.0001f;              // NaN limits: fmaxf keeps the other
+  cone.fn = mk3(0.0f, 0.0f, 0.0f);
+  cone.fe = e_pcf * 1.01f + 2.0e-5f;              // + the rounding of a probe direction off its plane
+  if (nprobe) {
+    const f3 fx = cross3(lightDir, mk3(0.57735026f, 0.57735026f, 0.57735026f));
+    const float f2 = dot3(fx, fx);
+    if (f2 > 1.0e-4f) cone.fn = fx * rsqrtf(f2);
+  }
   const float ll = dot3(lightDir, lightDir);
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
   const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin);
@@ -706,6 +742,9 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) r
   extern __shared__ float4 smem[];
   const DeviceScene& sc = kp.sc;
   const rt_frame_params& fp = kp.fp;
+#if RT_PK_STATS
+  g_stats = kp.counters;
+#endif
 
   // ---- stage the scene once per CTA: one contiguous copy of the host-built blob
   for (int i = threadIdx.x; i < sc.pk_float4s; i += kThreads) smem[i] = __ldg(sc.pk_blob + i);
