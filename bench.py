@@ -60,6 +60,9 @@ def parse_args():
     ap.add_argument("--height", type=int, default=None)
     ap.add_argument("--samples", type=int, default=None, help="override num_samples (config 4 defaults to 64)")
     ap.add_argument("--shard", choices=["samples", "rows"], default="samples")
+    ap.add_argument("--gather", choices=["peer", "nccl"], default="peer",
+                    help="--shard rows: peer = interleaved bands stored straight into rank 0's frame over NVLink (CUDA IPC); "
+                         "nccl = contiguous tiles gathered point to point")
     ap.add_argument("--flags", type=lambda s: int(s, 0), default=0, help="extra RT_FLAG_* bits (e.g. 0x2 parity math)")
     ap.add_argument("--host-path", type=int, default=0, help="rt_set_host_path: 0 auto, 1 staged, 2 banded, 3 zero-copy")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -206,6 +209,16 @@ def run_ours(args) -> None:
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        try:                                           # pinned host buffers first-touch on the GPU's NUMA node
+            import pynvml
+            pynvml.nvmlInit()
+            hnd = pynvml.nvmlDeviceGetHandleByIndex(local)
+            words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
+            cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+        except Exception:
+            pass
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -218,7 +231,13 @@ def run_ours(args) -> None:
     flags = args.flags
 
     # ---- sharding plan
-    if world > 1 and args.shard == "rows":
+    peer = None
+    if world > 1 and args.shard == "rows" and args.gather == "peer":
+        params = workload_params(w, flags=flags, **sharding.band_plan(rank, world))
+        peer = sharding.PeerFrame(ctx, H, W)
+        scaling, par = "strong", (f"interleaved {sharding.BAND_ROWS}-row bands x{world}, kernel stores go straight into "
+                                  "rank 0's frame over NVLink (CUDA IPC peer mapping), no gather")
+    elif world > 1 and args.shard == "rows":
         ra, rb = sharding.row_range(H, rank, world)
         params = workload_params(w, flags=flags, row_begin=ra, row_end=rb)
         scaling, par = "strong", f"row tiles x{world}, gathered to rank 0"
@@ -246,11 +265,15 @@ def run_ours(args) -> None:
 
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)   # > 126 MB L2
 
+    out = (peer.color, peer.position, peer.normal) if peer else (color, position if write_geom else None, normal if write_geom else None)
+
     def step():
         if params.flags & abi.FLAG_ACCUMULATE:
             color.zero_()
-        ctx.render(params, color, position if write_geom else None, normal if write_geom else None, None, stream.cuda_stream)
-        if world > 1 and args.shard == "rows":
+        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
+        if peer:
+            dist.barrier()                             # the frame is complete on rank 0 when every rank's kernel is
+        elif world > 1 and args.shard == "rows":
             for buf in (color, position, normal):
                 sharding.gather_rows(buf, H, world)
         elif world > 1:
@@ -275,9 +298,11 @@ def run_ours(args) -> None:
         ev[i][0].record(stream)
         if params.flags & abi.FLAG_ACCUMULATE:
             color.zero_()
-        ctx.render(params, color, position if write_geom else None, normal if write_geom else None, None, stream.cuda_stream)
+        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
         ev[i][1].record(stream)
-        if world > 1 and args.shard == "rows":
+        if peer:
+            dist.barrier()
+        elif world > 1 and args.shard == "rows":
             for buf in (color, position, normal):
                 sharding.gather_rows(buf, H, world)
         elif world > 1:
@@ -302,7 +327,11 @@ def run_ours(args) -> None:
     value = rays_total / (step_ms * 1e-3) / 1e6
 
     # ---- e2e through the C ABI with host buffers (rank-local frame; aggregate over ranks)
-    px = (params.row_end - params.row_begin) * W
+    if params.row_band > 0:
+        nb = (H + params.row_band - 1) // params.row_band
+        px = sum(min(params.row_band, H - k * params.row_band) for k in range(params.row_phase, nb, params.row_period)) * W
+    else:
+        px = (params.row_end - params.row_begin) * W
     h = {}
     for name, nbytes in (("color", px * 16), ("position", px * 16), ("normal", px * 8)):
         p = abi.C.c_void_p(0)
@@ -341,6 +370,11 @@ def run_ours(args) -> None:
         except Exception:
             pass
         ach_tf = flops_rank / (kern_ms * 1e-3) / 1e12
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{w.name}@{W}x{H}", {}).get("bytes")
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
@@ -352,7 +386,7 @@ def run_ours(args) -> None:
                        "math": "parity" if (flags & abi.FLAG_PARITY_MATH) else "fast"},
             "ms_per_frame": kern_ms,
             "roofline": {"bound": "fp32", "achieved": ach_tf, "peak": fp32_peak["tflops"], "unit": "TFLOP/s",
-                         "frac": ach_tf / fp32_peak["tflops"], "traffic": None,
+                         "frac": ach_tf / fp32_peak["tflops"], "traffic": traffic,
                          "peak_source": "measured in this run: FFMA-only micro-kernel (rt_measure_fp32_peak); "
                                         "MEASURED_PEAKS.json has no FP32 entry",
                          "algorithmic_flops_per_launch": flops_rank, "algorithmic_sfu_ops_per_launch": sfu_rank,
@@ -372,6 +406,10 @@ def run_ours(args) -> None:
             cb = cpu_baseline(w, kind, budget_s=12.0, step=args.cpu_sample_step)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
+    if peer:
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        peer.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

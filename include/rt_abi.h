@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* ------------------------------------------------------------------------- */
 /* Data contracts: byte-exact std430 layouts (== the alignas() C++ structs).   */
@@ -146,6 +146,10 @@ typedef struct rt_frame_params {
   int32_t  num_samples;          /* 1 = the reference; n = mean over frame_count..+n-1        */
   int32_t  max_ray_depth;        /* #define MAX_RAY_DEPTH 3 (glsl:4)                          */
   uint32_t flags;                /* RT_FLAG_*                                                 */
+  /* Interleaved row bands (multi-GPU load balance): row_band = 0 renders the whole
+   * window [row_begin,row_end); otherwise only the rows r of the window with
+   * ((r - row_begin) / row_band) % row_period == row_phase. row_band must be a multiple of 4. */
+  int32_t  row_band, row_period, row_phase;
 } rt_frame_params;
 
 /* Reference-literal operation counters (flop model v0). Index into
@@ -246,6 +250,16 @@ rt_status rt_render_gl(rt_context* ctx, const rt_frame_params* params,
 /* Counters accumulated by renders that carried RT_FLAG_COUNTERS since the last reset.
  * out must hold RT_CNT_COUNT uint64 values. Synchronises the context's device.     */
 rt_status rt_get_counters(rt_context* ctx, uint64_t* out, int reset);
+
+/* Device memory shared between the per-GPU processes of one box (cudaMalloc + CUDA IPC): the
+ * root rank allocates the frame, exports a 64-byte handle, every other rank opens it and passes
+ * the mapped address to rt_render — its stores then travel over NVLink into the root's frame
+ * (the "fused gather" of SURVEY 8e). rt_ipc_open returns a pointer valid in the caller's process. */
+rt_status rt_device_alloc(rt_context* ctx, void** out, size_t bytes);
+rt_status rt_device_free(rt_context* ctx, void* p);
+rt_status rt_ipc_export(rt_context* ctx, void* device_ptr, unsigned char handle[64]);
+rt_status rt_ipc_open(rt_context* ctx, const unsigned char handle[64], void** out);
+rt_status rt_ipc_close(rt_context* ctx, void* p);
 
 /* Pinned host memory helpers for the e2e path (cudaHostAlloc / cudaFreeHost). */
 rt_status rt_host_alloc(void** out, size_t bytes);

@@ -33,7 +33,8 @@ RT_CNT_COUNT = len(COUNTER_NAMES)
 EXPORTED_SYMBOLS = [
     "rt_abi_version", "rt_status_string", "rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene",
     "rt_set_skybox", "rt_set_noise", "rt_render", "rt_render_host", "rt_synchronize", "rt_render_gl",
-    "rt_get_counters", "rt_set_host_path", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
+    "rt_get_counters", "rt_set_host_path", "rt_device_alloc", "rt_device_free", "rt_ipc_export",
+    "rt_ipc_open", "rt_ipc_close", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
 ]
 
 
@@ -60,6 +61,7 @@ class FrameParams(C.Structure):
         ("noise_scale", C.c_float * 2),
         ("frame_count", C.c_int32), ("num_samples", C.c_int32), ("max_ray_depth", C.c_int32),
         ("flags", C.c_uint32),
+        ("row_band", C.c_int32), ("row_period", C.c_int32), ("row_phase", C.c_int32),
     ]
 
 
@@ -99,6 +101,11 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_render_gl.argtypes = [vp, C.POINTER(FrameParams), C.c_uint, C.c_uint, C.c_uint]
     lib.rt_get_counters.argtypes = [vp, C.POINTER(C.c_uint64), ip]
     lib.rt_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    lib.rt_device_alloc.argtypes = [vp, C.POINTER(vp), C.c_size_t]
+    lib.rt_device_free.argtypes = [vp, vp]
+    lib.rt_ipc_export.argtypes = [vp, vp, C.c_char_p]
+    lib.rt_ipc_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    lib.rt_ipc_close.argtypes = [vp, vp]
     lib.rt_host_free.argtypes = [vp]
     lib.rt_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(ip), C.POINTER(C.c_double)]
     lib.rt_launch_count.argtypes = [vp]

@@ -435,6 +435,8 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
     return fail(c, RT_ERR_INVALID_ARG, "rt_render: num_objects/num_lights exceed the uploaded scene");
   if (p->max_ray_depth < 0 || p->num_samples < 0) return fail(c, RT_ERR_INVALID_ARG, "rt_render: depth/samples");
   if (p->use_skybox && !c->d_sky) return fail(c, RT_ERR_INVALID_ARG, "rt_render: use_skybox without rt_set_skybox");
+  if (p->row_band < 0 || (p->row_band > 0 && (p->row_band % 4 != 0 || p->row_period <= 0 || p->row_phase < 0 || p->row_phase >= p->row_period)))
+    return fail(c, RT_ERR_INVALID_ARG, "rt_render: row_band must be a multiple of 4, 0 <= row_phase < row_period");
   if (p->row_begin == p->row_end) return RT_OK;
   RT_CUDA(c, cudaSetDevice(c->device));
   rt::KernelParams kp;
@@ -453,7 +455,14 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   kp.color = (float4*)d_color; kp.position = (float4*)d_position; kp.normal = d_normal; kp.object_id = d_object_id;
   kp.tile_counter = c->d_tile_counter; kp.tile_base = c->tile_base;
   kp.tiles_x = (unsigned)((p->width + 7) / 8);
-  kp.tiles_y = (unsigned)((p->row_end - p->row_begin + 3) / 4);
+  int local_rows = p->row_end - p->row_begin;
+  if (p->row_band > 0) {                                   // rows of the bands this caller owns
+    const int nbands = (local_rows + p->row_band - 1) / p->row_band;
+    const int mine = nbands > p->row_phase ? (nbands - p->row_phase + p->row_period - 1) / p->row_period : 0;
+    if (mine == 0) return RT_OK;
+    local_rows = mine * p->row_band;                       // the last band may be cut by row_end (checked per pixel)
+  }
+  kp.tiles_y = (unsigned)((local_rows + 3) / 4);
   const unsigned bty = (unsigned)rt::packet_block_tiles_y();
   kp.blocks_x = (kp.tiles_x + 3) / 4; kp.blocks_y = (kp.tiles_y + bty - 1) / bty;
   kp.counters = c->d_counters;
@@ -501,6 +510,8 @@ rt_status rt_render_host(rt_context* c, const rt_frame_params* p, const void* ob
   //             k+1 renders.
   //   STAGED    render the frame, then copy it (the v0 behaviour).
   int path = c->host_path;
+  if (p->row_band > 0 && path != RT_HOST_PATH_AUTO && path != RT_HOST_PATH_ZEROCOPY)
+    return fail(c, RT_ERR_INVALID_ARG, "rt_render_host: interleaved row bands need the zero-copy path");
   auto mapped = [](const void* h) -> bool {
     if (!h) return true;
     cudaPointerAttributes a;
@@ -510,6 +521,8 @@ rt_status rt_render_host(rt_context* c, const rt_frame_params* p, const void* ob
   const bool all_mapped = mapped(h_color) && mapped(h_position) && mapped(h_normal) && mapped(h_object_id);
   if (path == RT_HOST_PATH_AUTO) path = all_mapped ? RT_HOST_PATH_ZEROCOPY : RT_HOST_PATH_BANDED;   // measured: profiles/README.md
   if (path == RT_HOST_PATH_ZEROCOPY && !all_mapped) path = RT_HOST_PATH_STAGED;
+  if (p->row_band > 0 && path != RT_HOST_PATH_ZEROCOPY)
+    return fail(c, RT_ERR_INVALID_ARG, "rt_render_host: interleaved row bands need pinned, device-mapped host buffers");
   if (path == RT_HOST_PATH_ZEROCOPY) {
     st = rt_render(c, p, h_color, h_position, h_normal, h_object_id, c->stream);
     if (st != RT_OK) return st;
@@ -577,6 +590,42 @@ rt_status rt_get_counters(rt_context* c, uint64_t* out, int reset) {
   RT_CUDA(c, cudaDeviceSynchronize());
   RT_CUDA(c, cudaMemcpy(out, c->d_counters, sizeof(uint64_t) * RT_CNT_COUNT, cudaMemcpyDeviceToHost));
   if (reset) RT_CUDA(c, cudaMemset(c->d_counters, 0, sizeof(uint64_t) * RT_CNT_COUNT));
+  return RT_OK;
+}
+
+rt_status rt_device_alloc(rt_context* c, void** out, size_t bytes) {
+  if (!c || !out) return RT_ERR_INVALID_ARG;
+  RT_CUDA(c, cudaSetDevice(c->device));
+  RT_CUDA(c, cudaMalloc(out, bytes ? bytes : 1));
+  return RT_OK;
+}
+rt_status rt_device_free(rt_context* c, void* p) {
+  if (!c) return RT_ERR_INVALID_ARG;
+  RT_CUDA(c, cudaSetDevice(c->device));
+  RT_CUDA(c, cudaFree(p));
+  return RT_OK;
+}
+rt_status rt_ipc_export(rt_context* c, void* device_ptr, unsigned char handle[64]) {
+  if (!c || !device_ptr || !handle) return RT_ERR_INVALID_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  RT_CUDA(c, cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  RT_CUDA(c, cudaIpcGetMemHandle(&h, device_ptr));
+  std::memcpy(handle, &h, 64);
+  return RT_OK;
+}
+rt_status rt_ipc_open(rt_context* c, const unsigned char handle[64], void** out) {
+  if (!c || !handle || !out) return RT_ERR_INVALID_ARG;
+  RT_CUDA(c, cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, 64);
+  RT_CUDA(c, cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return RT_OK;
+}
+rt_status rt_ipc_close(rt_context* c, void* p) {
+  if (!c) return RT_ERR_INVALID_ARG;
+  RT_CUDA(c, cudaSetDevice(c->device));
+  RT_CUDA(c, cudaIpcCloseMemHandle(p));
   return RT_OK;
 }
 

@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(kThreads) rt_render_kernel(const __grid_consta
     if (lane == 0) next = atomicAdd(kp.tile_counter, 1u) - kp.tile_base;   // prefetch the next tile id
     const unsigned ty = tile / kp.tiles_x, txi = tile - ty * kp.tiles_x;
     const int px = (int)txi * kTileW + lx;
-    const int py = fp.row_begin + (int)ty * kTileH + ly;
+    const int py = window_row(fp, (int)ty * kTileH) + ly;
     if (px < fp.width && py < fp.row_end) {
       PixelResult r = shade_pixel<COUNT>(kp, s, tx, (unsigned)px, (unsigned)py, fp.frame_count, k);
       for (int sidx = 1; sidx < ns; ++sidx) {            // colour: sequential FP32 sum over samples

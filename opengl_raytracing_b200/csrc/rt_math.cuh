@@ -15,6 +15,14 @@ namespace rt {
 namespace RT_VARIANT_NS {
 
 constexpr float kPi = 3.14159265359f;            // glsl:6
+
+// Row of the frame for local row `lr` of this launch's tile grid (lr is a multiple of 4):
+// contiguous window, or interleaved bands (rt_frame_params.row_band / row_period / row_phase).
+__device__ __forceinline__ int window_row(const rt_frame_params& fp, int lr) {
+  if (fp.row_band <= 0) return fp.row_begin + lr;
+  const int k = lr / fp.row_band;
+  return fp.row_begin + (k * fp.row_period + fp.row_phase) * fp.row_band + (lr - k * fp.row_band);
+}
 // ---------------------------------------------------------------- small vector algebra
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 v; v.x = x; v.y = y; v.z = z; return v; }

@@ -805,7 +805,7 @@ __global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) r
     }
     const unsigned ty = tile / kp.tiles_x, txi = tile - ty * kp.tiles_x;
     const int px = (int)txi * kTileW + lx;
-    const int py = fp.row_begin + (int)ty * kTileH + ly;
+    const int py = window_row(fp, (int)ty * kTileH) + ly;
     const bool inside = tile < num_tiles && px < fp.width && py < fp.row_end;
     PixelResult r;                                       // position/normal/id: those of sample 0
 #pragma unroll 1

@@ -24,6 +24,10 @@ from . import scene as S
 def _ptr(a) -> C.c_void_p:
     if a is None:
         return C.c_void_p(0)
+    if isinstance(a, C.c_void_p):
+        return a                                   # raw device address (e.g. a peer-mapped frame)
+    if isinstance(a, int):
+        return C.c_void_p(a)
     if isinstance(a, np.ndarray):
         return C.c_void_p(a.ctypes.data)
     return C.c_void_p(int(a.data_ptr()))          # torch tensor
@@ -117,7 +121,8 @@ class RtContext:
 def frame_params(width: int, height: int, num_objects: int, num_lights: int, camera: S.Camera | None = None,
                  max_ray_depth: int = 3, frame_count: int = 0, num_samples: int = 1, use_skybox: bool = False,
                  row_begin: int = 0, row_end: int | None = None, flags: int = 0,
-                 noise_scale: float = 1.0 / 1024.0) -> abi.FrameParams:
+                 noise_scale: float = 1.0 / 1024.0, row_band: int = 0, row_period: int = 1,
+                 row_phase: int = 0) -> abi.FrameParams:
     """The uniform block of one dispatch with the reference's values: ``fov`` = Camera::FOV
     (45), ``focalLength`` 1.0 and ``maxRayDistance`` 114514.0 (shader defaults the host never
     overrides, glsl:80,85), ``noiseScale`` 1/1024 (src/ForwardShadingPipeline.cpp:164)."""
@@ -135,6 +140,7 @@ def frame_params(width: int, height: int, num_objects: int, num_lights: int, cam
     p.noise_scale[:] = (noise_scale, noise_scale)
     p.frame_count, p.num_samples, p.max_ray_depth = frame_count, num_samples, max_ray_depth
     p.flags = flags
+    p.row_band, p.row_period, p.row_phase = row_band, row_period, row_phase
     return p
 
 

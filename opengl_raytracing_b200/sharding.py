@@ -69,3 +69,76 @@ def reduce_samples(partial_sum, total_samples: int, dst: int = 0, group=None):
     partial_sum[..., :3] *= 1.0 / float(total_samples)
     partial_sum[..., 3] = 1.0
     return partial_sum
+
+
+# --------------------------------------------------------------------------- fused gather over NVLink
+BAND_ROWS = 32      # interleaved row bands: sky rows cost one ray per pixel, object rows dozens
+
+
+def band_plan(rank: int, world: int, band_rows: int = BAND_ROWS) -> dict:
+    """rt_frame_params fields for rank ``rank`` of ``world`` under interleaved row bands: band k of
+    the frame (``band_rows`` rows each) belongs to rank k % world."""
+    return {"row_band": band_rows, "row_period": world, "row_phase": rank}
+
+
+class _DevicePtr:
+    """Minimal __cuda_array_interface__ view of a raw device allocation (for torch.as_tensor)."""
+
+    def __init__(self, ptr: int, shape: tuple, typestr: str):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+class PeerFrame:
+    """The three output images of one frame, allocated on the root rank's GPU and mapped into every
+    other rank's address space through CUDA IPC (rt_device_alloc / rt_ipc_export / rt_ipc_open).
+    Each rank passes ``color`` / ``position`` / ``normal`` (plain device addresses) to rt_render:
+    the kernel's float4 stores then go straight into the root's frame over NVLink — the gather
+    disappears into the kernel epilogue (SURVEY.md 8e "fused form"). ``tensors()`` on the root
+    returns torch views of the frame."""
+
+    def __init__(self, ctx, height: int, width: int, root: int = 0, group=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        self.ctx, self.h, self.w, self.root = ctx, height, width, root
+        self.rank = dist.get_rank(group)
+        self.is_root = self.rank == root
+        sizes = {"color": height * width * 16, "position": height * width * 16, "normal": height * width * 8}
+        # the 64-byte IPC handles travel through the process group (CPU tensor under gloo)
+        dev = torch.device("cpu") if dist.get_backend(group) == "gloo" else torch.device("cuda", ctx.device)
+        handles = torch.zeros(3, 64, dtype=torch.uint8, device=dev)
+        self.ptr = {}
+        if self.is_root:
+            hs = []
+            for name, nbytes in sizes.items():
+                p = C.c_void_p(0)
+                ctx._check(ctx.lib.rt_device_alloc(ctx.handle, C.byref(p), nbytes))
+                buf = C.create_string_buffer(64)
+                ctx._check(ctx.lib.rt_ipc_export(ctx.handle, p, buf))
+                self.ptr[name] = p.value
+                hs.append(list(buf.raw))
+            handles.copy_(torch.tensor(hs, dtype=torch.uint8))
+        dist.broadcast(handles, src=root, group=group)
+        if not self.is_root:
+            hb = handles.cpu().numpy()
+            for i, name in enumerate(sizes):
+                p = C.c_void_p(0)
+                ctx._check(ctx.lib.rt_ipc_open(ctx.handle, hb[i].tobytes(), C.byref(p)))
+                self.ptr[name] = p.value
+        self.color, self.position, self.normal = (C.c_void_p(self.ptr[k]) for k in ("color", "position", "normal"))
+
+    def tensors(self):
+        import torch
+        assert self.is_root
+        c = torch.as_tensor(_DevicePtr(self.ptr["color"], (self.h, self.w, 4), "<f4"), device=f"cuda:{self.ctx.device}")
+        p = torch.as_tensor(_DevicePtr(self.ptr["position"], (self.h, self.w, 4), "<f4"), device=f"cuda:{self.ctx.device}")
+        n = torch.as_tensor(_DevicePtr(self.ptr["normal"], (self.h, self.w, 4), "<f2"), device=f"cuda:{self.ctx.device}")
+        return c, p, n
+
+    def close(self):
+        for name, p in self.ptr.items():
+            if self.is_root:
+                self.ctx.lib.rt_device_free(self.ctx.handle, p)
+            else:
+                self.ctx.lib.rt_ipc_close(self.ctx.handle, p)
+        self.ptr = {}

@@ -31,7 +31,7 @@ def test_library_loads_and_exports_every_symbol():
     lib = abi.load_library()
     for name in _declared_functions():
         assert hasattr(lib, name), name
-    assert lib.rt_abi_version() == 1
+    assert lib.rt_abi_version() == 2
     assert lib.rt_status_string(5) == b"RT_ERR_UNAVAILABLE"
 
 
@@ -44,7 +44,7 @@ def test_struct_layouts_against_c_compiler(tmp_path):
     fields += [("rt_light", f) for f in ("position", "direction", "color", "intensity", "radius", "samples",
                                           "shadowSoftness", "shadowType", "pcfSamples", "lightSize", "angularRadius")]
     fields += [("rt_frame_params", f) for f in ("row_begin", "camera_pos", "fov_deg", "use_skybox", "noise_scale",
-                                                 "frame_count", "num_samples", "max_ray_depth", "flags")]
+                                                 "frame_count", "num_samples", "max_ray_depth", "flags", "row_band", "row_period", "row_phase")]
     body = "".join(f'printf("{s}.{f} %zu\\n", offsetof({s}, {f}));\n' for s, f in fields)
     body += "".join(f'printf("sizeof.{s} %zu\\n", sizeof({s}));\n' for s in ("rt_object", "rt_material", "rt_light", "rt_aabb", "rt_frame_params"))
     src.write_text(f'#include <stdio.h>\n#include "{HEADER}"\nint main(void){{\n{body}return 0;}}\n')

@@ -176,6 +176,45 @@ def test_row_tile_sharding_is_bit_identical(rt_ctx):
     assert np.array_equal(oid.cpu().numpy(), full["object_id"])
 
 
+@pytest.mark.parametrize("n,world,band", [(2, 3, 32), (3, 8, 32), (5, 4, 8)])
+def test_interleaved_row_bands_are_bit_identical(rt_ctx, n, world, band):
+    """SURVEY 8e load balance: rank g renders bands g, g+G, ... (row_band/row_period/row_phase);
+    the union over the ranks == the unsharded render, bit for bit, for both kernels."""
+    import torch
+    w = synthetic.config(n, 320, 200)
+    bind_workload(rt_ctx, w)
+    full = render_workload(rt_ctx, w, bind=False)
+    H, W = w.height, w.width
+    for extra in (0, abi.FLAG_LITERAL_KERNEL):
+        color = torch.full((H, W, 4), -7.0, device="cuda"); pos = torch.zeros(H, W, 4, device="cuda")
+        nrm = torch.zeros(H, W, 4, dtype=torch.float16, device="cuda"); oid = torch.full((H, W), -9, dtype=torch.int32, device="cuda")
+        for g in range(world):
+            p = workload_params(w, flags=extra, row_band=band, row_period=world, row_phase=g)
+            rt_ctx.render(p, color, pos, nrm, oid, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        if extra == 0:
+            assert np.array_equal(color.cpu().numpy().view(np.uint32), full["color"].view(np.uint32))
+            assert np.array_equal(pos.cpu().numpy().view(np.uint32), full["position"].view(np.uint32))
+        assert np.array_equal(oid.cpu().numpy(), full["object_id"])
+        assert np.array_equal(nrm.float().cpu().numpy(), full["normal"])
+
+
+def test_peer_frame_over_cuda_ipc_two_processes(tmp_path):
+    """The fused gather: two rank processes (gloo for the plumbing; both on cuda:0 when the box has
+    one GPU) render interleaved bands straight into rank 0's IPC-shared frame; rank 0 checks the
+    frame against its own unsharded render, bit for bit."""
+    import subprocess
+    import torch
+    here = os.path.dirname(os.path.abspath(__file__))
+    script = os.path.join(here, "peer_frame_worker.py")
+    port = 29600 + os.getpid() % 300
+    env = dict(os.environ, PEER_GPUS=str(min(2, torch.cuda.device_count())))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), script],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "PEER_FRAME_OK" in r.stdout, (r.stdout[-2000:], r.stderr[-3000:])
+
+
 def test_sample_range_sharding_sums_to_the_mean(rt_ctx):
     """per-range partial sums (RT_FLAG_ACCUMULATE), added in range order, * 1/n ==
     the single-launch mean within FP32 summation error."""
