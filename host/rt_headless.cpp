@@ -1,0 +1,126 @@
+// rt_headless — the reference's frame loop without a window (src/main.cpp + the ray-tracing slice
+// of ForwardShadingPipline::Render), on top of host/rt_host.hpp and librt_b200.so.
+//
+//   rt_headless --scene default.scene --size 1920 1080 --frames 4 --out /tmp/frame
+//   rt_headless --dump-scene in.scene out.bin        (SceneIO only; needs no GPU)
+//   rt_headless --resave in.scene out.scene          (Load + Save round trip; needs no GPU)
+//
+// Outputs (row 0 = GL y 0): <out>_color.pfm, and with --raw also <out>_color.f32, <out>_position.f32
+// (RGBA32F) and <out>_normal.f16 (RGBA16F) — the three images the reference's post chain consumes.
+#include <chrono>
+#include <cstdlib>
+#include <iostream>
+
+#include "rt_host.hpp"
+
+using namespace rtb200;
+
+static int usage() {
+  std::fprintf(stderr,
+               "usage: rt_headless --scene FILE [--size W H] [--frames N] [--depth D] [--samples S] [--flags F]\n"
+               "                   [--camera px py pz yaw pitch fov] [--noise FILE W H] [--skybox FILE SIZE CH f16|f32]\n"
+               "                   [--device N] [--out PREFIX] [--raw]\n"
+               "       rt_headless --dump-scene IN.scene OUT.bin\n"
+               "       rt_headless --resave IN.scene OUT.scene\n");
+  return 2;
+}
+
+static int dump_scene(const char* in, const char* out) {
+  std::vector<Object> objects;
+  std::vector<Light> lights;
+  SceneNames names;
+  if (!SceneIO::Load(in, objects, lights, &names)) { std::fprintf(stderr, "cannot open %s\n", in); return 1; }
+  // int32 n_objects, int32 n_lights, Object[n], Light[m]
+  std::vector<unsigned char> blob(8 + objects.size() * sizeof(Object) + lights.size() * sizeof(Light));
+  const int32_t n = (int32_t)objects.size(), m = (int32_t)lights.size();
+  std::memcpy(blob.data(), &n, 4);
+  std::memcpy(blob.data() + 4, &m, 4);
+  if (n) std::memcpy(blob.data() + 8, objects.data(), objects.size() * sizeof(Object));
+  if (m) std::memcpy(blob.data() + 8 + objects.size() * sizeof(Object), lights.data(), lights.size() * sizeof(Light));
+  if (!WriteRaw(out, blob.data(), blob.size())) { std::fprintf(stderr, "cannot write %s\n", out); return 1; }
+  for (const auto& s : names.objects) std::printf("OBJECT %s\n", s.c_str());
+  for (const auto& s : names.lights) std::printf("LIGHT %s\n", s.c_str());
+  return 0;
+}
+
+static int resave(const char* in, const char* out) {
+  std::vector<Object> objects;
+  std::vector<Light> lights;
+  SceneNames names;
+  if (!SceneIO::Load(in, objects, lights, &names)) { std::fprintf(stderr, "cannot open %s\n", in); return 1; }
+  return SceneIO::Save(out, objects, lights, &names) ? 0 : 1;
+}
+
+int main(int argc, char** argv) {
+  if (argc >= 4 && std::string(argv[1]) == "--dump-scene") return dump_scene(argv[2], argv[3]);
+  if (argc >= 4 && std::string(argv[1]) == "--resave") return resave(argv[2], argv[3]);
+
+  std::string scene, out = "frame", noise_file, sky_file;
+  int W = 800, H = 800, frames = 1, depth = 3, samples = 1, device = 0;   // src/global.cpp:4-5: 800 x 800
+  int noise_w = 0, noise_h = 0, sky_size = 0, sky_ch = 4;
+  bool sky_f16 = true, raw = false, have_cam = false;
+  unsigned flags = 0;
+  float cam[6] = {0, 0, 0, -90, 0, 45};
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    auto need = [&](int k) { if (i + k >= argc) { usage(); std::exit(2); } };
+    if (a == "--scene") { need(1); scene = argv[++i]; }
+    else if (a == "--size") { need(2); W = std::atoi(argv[++i]); H = std::atoi(argv[++i]); }
+    else if (a == "--frames") { need(1); frames = std::atoi(argv[++i]); }
+    else if (a == "--depth") { need(1); depth = std::atoi(argv[++i]); }
+    else if (a == "--samples") { need(1); samples = std::atoi(argv[++i]); }
+    else if (a == "--flags") { need(1); flags = (unsigned)std::strtoul(argv[++i], nullptr, 0); }
+    else if (a == "--device") { need(1); device = std::atoi(argv[++i]); }
+    else if (a == "--out") { need(1); out = argv[++i]; }
+    else if (a == "--raw") raw = true;
+    else if (a == "--camera") { need(6); for (int k = 0; k < 6; ++k) cam[k] = (float)std::atof(argv[++i]); have_cam = true; }
+    else if (a == "--noise") { need(3); noise_file = argv[++i]; noise_w = std::atoi(argv[++i]); noise_h = std::atoi(argv[++i]); }
+    else if (a == "--skybox") { need(4); sky_file = argv[++i]; sky_size = std::atoi(argv[++i]); sky_ch = std::atoi(argv[++i]); sky_f16 = std::string(argv[++i]) == "f16"; }
+    else return usage();
+  }
+  if (scene.empty()) return usage();
+
+  try {
+    ForwardShadingPipeline pipeline(W, H, device);
+    if (!pipeline.LoadScene(scene)) { std::fprintf(stderr, "cannot open %s\n", scene.c_str()); return 1; }
+    if (!noise_file.empty()) {
+      const std::vector<unsigned char> n = ReadRaw(noise_file);
+      if (n.size() != (size_t)noise_w * noise_h) throw std::runtime_error("noise file size != W*H");
+      pipeline.SetNoise(n.data(), noise_w, noise_h);
+    }
+    if (!sky_file.empty()) {
+      const std::vector<unsigned char> s = ReadRaw(sky_file);
+      if (s.size() != (size_t)6 * sky_size * sky_size * sky_ch * (sky_f16 ? 2 : 4)) throw std::runtime_error("skybox file size");
+      pipeline.SetSkybox(s.data(), sky_size, sky_ch, sky_f16);
+    }
+    if (have_cam) {
+      pipeline.camera.Position = v3(cam[0], cam[1], cam[2]);
+      pipeline.camera.Yaw = cam[3]; pipeline.camera.Pitch = cam[4]; pipeline.camera.FOV = cam[5];
+      pipeline.camera.UpdateVectors();
+    }
+    pipeline.maxRayDepth = depth;
+    pipeline.numSamples = samples;
+    pipeline.flags = flags;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int f = 0; f < frames; ++f) pipeline.Render();
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    std::printf("{\"scene\": \"%s\", \"objects\": %zu, \"lights\": %zu, \"width\": %d, \"height\": %d, \"frames\": %d, "
+                "\"ms_per_frame_host\": %.4f, \"launches\": %llu}\n",
+                scene.c_str(), pipeline.ssbo.objects.size(), pipeline.lightSSBO.lights.size(), W, H, frames, ms / frames,
+                (unsigned long long)rt_launch_count(pipeline.context()));
+    const size_t px = (size_t)W * H;
+    if (!WritePFM(out + "_color.pfm", pipeline.outputTex.data(), W, H)) throw std::runtime_error("cannot write " + out + "_color.pfm");
+    if (raw) {
+      const bool n32 = (flags & RT_FLAG_NORMAL_FP32) != 0;
+      if (n32) throw std::runtime_error("--raw with RT_FLAG_NORMAL_FP32: the pipeline's normal image is RGBA16F");
+      if (!WriteRaw(out + "_color.f32", pipeline.outputTex.data(), px * 16) ||
+          !WriteRaw(out + "_position.f32", pipeline.gPositionTex.data(), px * 16) ||
+          !WriteRaw(out + "_normal.f16", pipeline.gNormalTex.data(), px * 8))
+        throw std::runtime_error("cannot write raw outputs");
+    }
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "rt_headless: %s\n", e.what());
+    return 1;
+  }
+  return 0;
+}

@@ -58,7 +58,26 @@ def build(force: bool = False, verbose: bool = False, variant: str = "", defines
     return lib
 
 
+HOST_DIR = os.path.join(HERE, "..", "host")
+HEADLESS = os.path.join(HOST_DIR, "rt_headless")
+
+
+def build_host(force: bool = False) -> str:
+    """host/rt_headless: the C++ host layer (host/rt_host.hpp) + the windowless frame loop, linked
+    against csrc/librt_b200.so through an $ORIGIN-relative rpath (so it runs on the GPU box)."""
+    src = [os.path.join(HOST_DIR, "rt_headless.cpp"), os.path.join(HOST_DIR, "rt_host.hpp"),
+           os.path.join(HERE, "..", "include", "rt_abi.h"), LIB]
+    if force or _stale(HEADLESS, src):
+        cmd = [os.environ.get("CXX", "g++"), "-std=c++17", "-O2", "-Wall", "-ffp-contract=off",
+               "-I" + os.path.join(HERE, "..", "include"), "-I" + HOST_DIR, src[0], "-o", HEADLESS,
+               "-L" + CSRC, "-lrt_b200", "-Wl,-rpath,$ORIGIN/../opengl_raytracing_b200/csrc"]
+        subprocess.run(cmd, check=True)
+    return HEADLESS
+
+
 if __name__ == "__main__":
     args = [a for a in sys.argv[1:] if not a.startswith("-")]
     print(build(force="-f" in sys.argv, verbose="-v" in sys.argv, variant=args[0] if args else "",
                 defines=tuple(args[1:])))
+    if not args:
+        print(build_host(force="-f" in sys.argv))

@@ -5,7 +5,8 @@ Mirrors, in the reference's own vocabulary:
         (/root/reference/src/Object.h:8-21, src/Material.h:11-23, src/Light.h:7-20)
   * ``SceneIO::Load`` / ``ParseObject`` / ``ParseLight`` (src/SceneIO.h:108-122,145-186),
     including the C++ ``istream >>`` extraction semantics the shipped scene files rely on
-    (a failed extraction stores 0 and sets failbit; later extractions are no-ops)
+    (a malformed field stores 0 and sets failbit; a missing field, or any field after a
+    failure, keeps its default)
   * ``GenerateAABBForObject`` (src/SceneIO.h:75-104), evaluated in FP32 exactly as glm does
   * ``Camera`` defaults and ``UpdateVectors`` (src/Camera.h:9-34)
 
@@ -171,11 +172,15 @@ class _IStream:
         return w
 
     def _num(self, rx, conv, default):
-        """Returns the extracted value; on failure 0 (C++11) — or ``default`` untouched
-        when the stream had already failed."""
+        """Returns the extracted value. A field that is present but not a number stores 0
+        (C++11 num_get) and sets failbit; when the line has simply run out (the sentry hits
+        end-of-stream) or the stream had already failed, nothing is stored: ``default`` stays."""
         if self.fail:
             return default
         self._skip()
+        if self.i >= len(self.s):
+            self.fail = True
+            return default
         m = rx.match(self.s, self.i)
         if not m:
             self.fail = True

@@ -26,7 +26,7 @@ def test_sphere_and_plane_aabbs():
 
 
 def test_parser_stream_semantics():
-    text = ("OBJECT SPHERE A 1 2 3 0.5 0 0 0 0 0 1 0.1 0.2 0.3 0.4 0.5 1.5 0.9\n"      # one token short: specular <- 0
+    text = ("OBJECT SPHERE A 1 2 3 0.5 0 0 0 0 0 1 0.1 0.2 0.3 0.4 0.5 1.5 0.9\n"      # one token short: specular keeps its default
             "\n"
             "OBJECT PLANE G 0 -1 0 0 0 1 0 4 6 0 0.8 0.8 0.8 0 0 1 0 0\n"
             "LIGHT AREA L 0 3 0 0 -1 0 1 1 0.9 5 0.5 16\n"
@@ -37,7 +37,7 @@ def test_parser_stream_semantics():
     assert a["type"] == S.SPHERE and tuple(a["position"]) == (1, 2, 3) and a["radius"] == np.float32(0.5)
     m = a["material"]
     assert m["type"] == 1 and np.allclose(m["albedo"], (0.1, 0.2, 0.3)) and m["metallic"] == np.float32(0.4)
-    assert m["ior"] == np.float32(1.5) and m["transparency"] == np.float32(0.9) and m["specular"] == 0.0
+    assert m["ior"] == np.float32(1.5) and m["transparency"] == np.float32(0.9) and m["specular"] == np.float32(0.5)
     assert m["diffuseStrength"] == 0.0 and m["scatterDistance"] == np.float32(0.1)   # q3 defaults
     assert sc.lights[0]["type"] == S.AREA and sc.lights[1]["type"] == S.POINT
     assert sc.lights[0]["shadowType"] == S.SHADOW_PCF and sc.lights[0]["pcfSamples"] == 4   # q5 defaults
@@ -69,9 +69,9 @@ def test_shipped_scenes_decode_like_golden(name, nobj, nlights):
 def test_performance_scene_short_lines():
     g = np.load(os.path.join(GOLDEN, "scenes.npz"))
     objs = g["performance_test_objects"].view(S.OBJECT_DTYPE)
-    glass = objs[7]                       # "Glass1": one token short -> specular <- 0 (failed extraction)
+    glass = objs[7]                       # "Glass1": one token short: the sentry hits end-of-line, specular keeps 0.5
     m = glass["material"]
-    assert m["specular"] == 0.0 and m["ior"] == 0.0 and m["transparency"] == np.float32(0.95)
+    assert m["specular"] == np.float32(0.5) and m["ior"] == 0.0 and m["transparency"] == np.float32(0.95)
 
 
 def test_camera_defaults_and_update_vectors():
