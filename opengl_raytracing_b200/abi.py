@@ -65,6 +65,19 @@ class FrameParams(C.Structure):
     ]
 
 
+class PostParams(C.Structure):
+    """rt_post_params (include/rt_post.h): the post chain's uniforms, src/ForwardShadingPipeline.cpp:185-254."""
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32),
+        ("bloom_threshold", C.c_float), ("bloom_strength", C.c_float),
+        ("blur_passes", C.c_int32), ("taa_enabled", C.c_int32),
+        ("taa_blend", C.c_float), ("jitter_x", C.c_float), ("jitter_y", C.c_float),
+        ("flags", C.c_uint32),
+    ]
+
+
+POST_LITERAL_PASSES = 0x01
+
 _lib = None
 
 
@@ -110,6 +123,19 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(ip), C.POINTER(C.c_double)]
     lib.rt_launch_count.argtypes = [vp]
     lib.rt_launch_count.restype = C.c_uint64
+    # include/rt_post.h
+    pp = C.POINTER(PostParams)
+    lib.rt_generate_aabbs.argtypes = [vp, vp, ip]
+    lib.rt_generate_aabbs_device.argtypes = [vp, vp, ip, vp]
+    lib.rt_decode_rgbe.argtypes = [vp, vp, vp, C.c_size_t, vp]
+    lib.rt_equirect_to_cubemap.argtypes = [vp, vp, ip, ip, vp, ip, vp]
+    lib.rt_bloom_extract.argtypes = [vp, pp, vp, vp, vp]
+    lib.rt_gaussian_blur.argtypes = [vp, pp, vp, vp, ip, vp]
+    lib.rt_bloom_combine.argtypes = [vp, pp, vp, vp, vp, vp]
+    lib.rt_taa_resolve.argtypes = [vp, pp, vp, vp, vp, vp, vp]
+    lib.rt_post_chain.argtypes = [vp, pp, vp, vp, vp, vp, vp, vp]
+    lib.rt_post_launch_count.argtypes = [vp]
+    lib.rt_post_launch_count.restype = C.c_uint64
     if path is None:
         _lib = lib
     return lib

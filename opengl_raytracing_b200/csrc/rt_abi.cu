@@ -48,6 +48,7 @@ struct rt_context {
   float4* o_color = nullptr; float4* o_position = nullptr; void* o_normal = nullptr; int* o_id = nullptr;
   size_t o_pixels = 0;
   bool tables_uploaded = false;
+  void* post_state = nullptr;   // rt_post.cu
 };
 
 namespace {
@@ -60,6 +61,15 @@ rt_status cuda_fail(rt_context* c, cudaError_t e, const char* what) {
   rt_status s = (e == cudaErrorMemoryAllocation) ? RT_ERR_OOM : RT_ERR_CUDA;
   return fail(c, s, std::string(what) + ": " + cudaGetErrorString(e));
 }
+}  // namespace
+
+namespace rt {
+int ctx_device(rt_context* c) { return c->device; }
+rt_status ctx_fail(rt_context* c, rt_status s, const std::string& msg) { return fail(c, s, msg); }
+void** ctx_post_slot(rt_context* c) { return &c->post_state; }
+}  // namespace rt
+
+namespace {
 #define RT_CUDA(ctx, call)                                         \
   do {                                                             \
     cudaError_t e__ = (call);                                      \
@@ -309,6 +319,7 @@ void rt_destroy(rt_context* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  rt::post_release(c->post_state);
   if (c->sky_tex) cudaDestroyTextureObject(c->sky_tex);
   if (c->sky_array) cudaFreeArray(c->sky_array);
   cudaFree(c->d_sky); cudaFree(c->d_noise); cudaFree(c->d_scene);

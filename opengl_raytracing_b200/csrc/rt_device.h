@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string>
 #include "../../include/rt_abi.h"
 
 namespace rt {
@@ -83,5 +84,12 @@ cudaError_t launch_packet_parity(const KernelParams& kp, int sm_count, cudaStrea
 // halton2/halton3: 64 entries each; probe_order: the 16 PCSS probe indices sorted by offset
 cudaError_t upload_tables_fast(const float* halton2, const float* halton3, const int* probe_order);
 cudaError_t upload_tables_parity(const float* halton2, const float* halton3, const int* probe_order);
+
+// Hooks between rt_abi.cu (owner of rt_context) and rt_post.cu (the f1-f3 stages keep their
+// per-context state behind one opaque slot; rt_destroy releases it through post_release).
+int ctx_device(rt_context* c);
+rt_status ctx_fail(rt_context* c, rt_status s, const std::string& msg);
+void** ctx_post_slot(rt_context* c);
+void post_release(void* state);
 
 }  // namespace rt

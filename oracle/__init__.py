@@ -123,3 +123,119 @@ def render(w, kind: str = "port", x0: int = 0, y0: int = 0, sx: int = 1, sy: int
         raise RuntimeError(f"oracle_render({kind}) failed: {rc}")
     return {"color": color, "position": position, "normal": normal, "object_id": object_id,
             "counters": {k: int(counters[i]) for i, k in enumerate(abi.COUNTER_NAMES)}}
+
+
+# --------------------------------------------------------------------------- f1-f3 stages (post_api.h)
+POST_PORT_SO = os.path.join(HERE, "librt_post_oracle.so")
+POST_REF_SO = os.path.join(HERE, "_ref", "libref_post.so")
+
+
+def build_post_port(force: bool = False) -> str:
+    src = os.path.join(HERE, "post_oracle.cpp")
+    deps = [src, os.path.join(HERE, "post_api.h"), os.path.join(HERE, "..", "include", "rt_abi.h")]
+    if not force and os.path.isfile(POST_PORT_SO) and all(os.path.getmtime(POST_PORT_SO) >= os.path.getmtime(d) for d in deps):
+        return POST_PORT_SO
+    subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-fno-fast-math", "-fPIC",
+                    "-shared", "-Wall", "-o", POST_PORT_SO, src], check=True)
+    _libs.pop("post_port", None)
+    return POST_PORT_SO
+
+
+def build_post_ref(force: bool = False) -> str | None:
+    """oracle/_ref/libref_post.so from the reference's fragment shaders, when the tree is present."""
+    from . import make_ref
+    srcs = make_ref.post_sources()
+    if not all(os.path.isfile(f) for f in srcs):
+        return POST_REF_SO if os.path.isfile(POST_REF_SO) else None
+    deps = srcs + [os.path.join(HERE, f) for f in ("post_harness.cpp", "post_shim.h", "glsl_shim.h", "post_api.h", "make_ref.py")]
+    if not force and os.path.isfile(POST_REF_SO) and all(os.path.getmtime(POST_REF_SO) >= os.path.getmtime(d) for d in deps):
+        return POST_REF_SO
+    make_ref.build_post()
+    _libs.pop("post_reference", None)
+    return POST_REF_SO
+
+
+def have_post(kind: str) -> bool:
+    return os.path.isfile(POST_PORT_SO if kind == "port" else POST_REF_SO)
+
+
+def load_post(kind: str = "port") -> C.CDLL:
+    key = "post_" + kind
+    if key in _libs:
+        return _libs[key]
+    if kind == "port" and not os.path.isfile(POST_PORT_SO):
+        build_post_port()
+    lib = C.CDLL(POST_PORT_SO if kind == "port" else POST_REF_SO)
+    lib.post_oracle_kind.restype = C.c_char_p
+    vp, ip, fl = C.c_void_p, C.c_int, C.c_float
+    lib.post_bloom_extract.argtypes = [vp, ip, ip, fl, vp]
+    lib.post_gaussian_blur.argtypes = [vp, ip, ip, ip, vp]
+    lib.post_bloom_combine.argtypes = [vp, vp, ip, ip, fl, vp]
+    lib.post_taa.argtypes = [vp, vp, vp, ip, ip, fl, fl, fl, vp]
+    lib.post_equirect_to_cubemap.argtypes = [vp, ip, ip, ip, vp]
+    lib.post_generate_aabbs.argtypes = [vp, ip]
+    lib.post_decode_rgbe.argtypes = [vp, C.c_size_t, vp]
+    assert lib.post_oracle_kind().decode() == kind
+    _libs[key] = lib
+    return lib
+
+
+def _img(a: np.ndarray, ch: int = 4) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    assert a.ndim == 3 and a.shape[2] == ch, a.shape
+    return a
+
+
+class Post:
+    """numpy front end of one post oracle ("port" or "reference"). RGBA16F images are float32
+    arrays holding half-rounded values."""
+
+    def __init__(self, kind: str = "port"):
+        self.kind, self.lib = kind, load_post(kind)
+
+    def bloom_extract(self, color, threshold=1.0):
+        color = _img(color); out = np.empty_like(color)
+        assert self.lib.post_bloom_extract(color.ctypes.data, color.shape[1], color.shape[0], threshold, out.ctypes.data) == 0
+        return out
+
+    def gaussian_blur(self, img, horizontal: bool):
+        img = _img(img); out = np.empty_like(img)
+        assert self.lib.post_gaussian_blur(img.ctypes.data, img.shape[1], img.shape[0], 1 if horizontal else 0, out.ctypes.data) == 0
+        return out
+
+    def bloom_combine(self, color, bloom, strength=0.5):
+        color, bloom = _img(color), _img(bloom); out = np.empty_like(color)
+        assert self.lib.post_bloom_combine(color.ctypes.data, bloom.ctypes.data, color.shape[1], color.shape[0], strength, out.ctypes.data) == 0
+        return out
+
+    def taa(self, color, history, normal, blend, jx, jy):
+        color, history, normal = _img(color), _img(history), _img(normal); out = np.empty_like(color)
+        assert self.lib.post_taa(color.ctypes.data, history.ctypes.data, normal.ctypes.data, color.shape[1], color.shape[0],
+                                 blend, jx, jy, out.ctypes.data) == 0
+        return out
+
+    def post_chain(self, color, normal, history, threshold=1.0, strength=0.5, passes=10, taa=True, blend=0.1, jx=0.0, jy=0.0):
+        """src/ForwardShadingPipeline.cpp:185-254 -> (display, new history or None)."""
+        a = self.bloom_extract(color, threshold)
+        horizontal = True
+        for _ in range(passes):
+            a = self.gaussian_blur(a, horizontal)
+            horizontal = not horizontal
+        display = self.bloom_combine(color, a, strength)
+        return display, (self.taa(color, history, normal, blend, jx, jy) if taa else None)
+
+    def equirect_to_cubemap(self, equirect_rgb, face_size):
+        e = _img(equirect_rgb, 3); out = np.empty((6, face_size, face_size, 4), np.float32)
+        assert self.lib.post_equirect_to_cubemap(e.ctypes.data, e.shape[1], e.shape[0], face_size, out.ctypes.data) == 0
+        return out
+
+    def generate_aabbs(self, objects: np.ndarray) -> np.ndarray:
+        o = np.frombuffer(bytearray(np.ascontiguousarray(objects).tobytes()), dtype=objects.dtype)   # keeps the padding bytes
+        assert self.lib.post_generate_aabbs(o.ctypes.data, len(o)) == 0, "port only"
+        return o
+
+    def decode_rgbe(self, rgbe: np.ndarray) -> np.ndarray:
+        q = np.ascontiguousarray(rgbe, dtype=np.uint8).reshape(-1, 4)
+        out = np.empty((len(q), 3), np.float32)
+        assert self.lib.post_decode_rgbe(q.ctypes.data, len(q), out.ctypes.data) == 0, "port only"
+        return out

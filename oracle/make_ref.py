@@ -18,6 +18,12 @@ Rewrite rules (each a regex; nothing is re-derived or re-ordered):
   7. `imageSize(outputImage)` -> `imageSize_(outputImage)` (a local shadows the builtin)
   8. `void main()` -> `void shader_main()`
   9. `#define MAX_RAY_DEPTH n` -> `int MAX_RAY_DEPTH = n;` (run-time)
+
+The fragment shaders of the stages either side of the path (bloom, TAA, equirect -> cube; built
+into oracle/_ref/libref_post.so against post_shim.h + post_harness.cpp) take the same rules plus:
+ 10. global-scope `in T x;` / `out T x;`  ->  `thread_local T x;` (stage inputs / outputs)
+ 11. `T name[n] = T[] (a, b, ...);`  ->  `T name[n] = {a, b, ...};`
+ 12. `ivec2(gl_FragCoord)`  ->  `to_ivec2(gl_FragCoord)` (a vec4 -> ivec2 constructor)
 """
 import os
 import re
@@ -61,6 +67,55 @@ def rewrite(src: str) -> str:
     return src
 
 
+def rewrite_fragment(src: str) -> str:
+    src = re.sub(r"//[^\n]*", "", src)
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = re.sub(r"layout\s*\([^)]*\)\s*", "", src)                                       # rule 3 (first half)
+    src = re.sub(r"^\s*(?:in|out)\s+(\w+)\s+(\w+)\s*;", r"thread_local \1 \2;", src, flags=re.M)   # rule 10
+    src = re.sub(r"(\w+)\s+(\w+)\s*\[\s*(\d+)\s*\]\s*=\s*\1\s*\[\s*\]\s*\(([^)]*)\)\s*;",
+                 r"\1 \2[\3] = {\4};", src)                                              # rule 11
+    src = src.replace("ivec2(gl_FragCoord)", "to_ivec2(gl_FragCoord)")                    # rule 12
+    return rewrite(src)
+
+
+POST_SHADERS = {                      # macro -> file under /root/reference/shader
+    "EXTRACT_INC": "brightness_extractFS.glsl",
+    "BLUR_INC": "gaussian_blurFs.glsl",
+    "COMBINE_INC": "bloom_combineFs.glsl",
+    "TAA_INC": "taaFs.glsl",
+    "SKYBOX_INC": "skyboxFs.glsl",
+}
+OUT_POST_SO = os.path.join(OUT_DIR, "libref_post.so")
+
+
+def post_sources() -> list:
+    d = os.path.dirname(REF_SHADER)
+    return [os.path.join(d, f) for f in POST_SHADERS.values()]
+
+
+def build_post(verbose: bool = False) -> str:
+    for f in post_sources():
+        if not os.path.isfile(f):
+            raise FileNotFoundError(f"reference shader not found: {f}")
+    os.makedirs(OUT_DIR, exist_ok=True)
+    with tempfile.TemporaryDirectory(prefix="rtref_") as tmp:
+        defs = []
+        for (macro, name), path in zip(POST_SHADERS.items(), post_sources()):
+            with open(path, encoding="utf-8", errors="replace") as f:
+                text = f.read()
+            inc = os.path.join(tmp, name + ".inc")
+            with open(inc, "w") as f:
+                f.write(rewrite_fragment(text))
+            defs.append(f'-D{macro}="{inc}"')
+        cmd = ["g++", "-O2", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-fPIC", "-shared",
+               "-fno-fast-math", "-Wno-unused-variable"] + defs + ["-I", HERE,
+               os.path.join(HERE, "post_harness.cpp"), "-o", OUT_POST_SO]
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.run(cmd, check=True)
+    return OUT_POST_SO
+
+
 def build(verbose: bool = False) -> str:
     if not os.path.isfile(REF_SHADER):
         raise FileNotFoundError(f"reference shader not found: {REF_SHADER}")
@@ -83,3 +138,4 @@ def build(verbose: bool = False) -> str:
 
 if __name__ == "__main__":
     print(build(verbose="-v" in sys.argv))
+    print(build_post(verbose="-v" in sys.argv))

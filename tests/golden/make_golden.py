@@ -3,6 +3,8 @@
 
   scenes.npz  the three shipped scene files decoded by this repo's restatement of SceneIO
               (the reference tree is absent on the GPU box)
+  post.npz    bloom / TAA / equirect->cube outputs of oracle/_ref/libref_post.so (the reference's
+              fragment shaders compiled as C++) on seeded inputs
   tiles.npz   colour / position / normal of small renders produced by oracle/_ref — the
               reference's OWN shader source compiled as C++ — for the five BASELINE configs,
               the shipped scenes and the edge cases. These pin the port (tests/test_oracle.py).
@@ -52,6 +54,29 @@ def main():
             tiles[f"{name}.{k}"] = r[k]
     np.savez_compressed(os.path.join(HERE, "tiles.npz"), **tiles)
     print("wrote", len(scenes), "scene arrays and", len(tiles), "tile arrays")
+    post_golden()
+
+
+def post_golden():
+    """post.npz: outputs of oracle/_ref/libref_post.so (the reference's fragment shaders compiled
+    as C++) on the seeded inputs of tests/test_post_oracle.py::post_inputs."""
+    from test_post_oracle import post_inputs
+    from opengl_raytracing_b200 import post as P
+    oracle.build_post_ref(force=True)
+    R = oracle.Post("reference")
+    color, normal, history = post_inputs()
+    h, w = color.shape[:2]
+    jx, jy = P.taa_jitter(3, w, h)
+    g = {"jitter": np.array([jx, jy], np.float64)}
+    g["extract"] = R.bloom_extract(color, 1.0)
+    g["blur_h"] = R.gaussian_blur(g["extract"], True)
+    g["blur_v"] = R.gaussian_blur(g["extract"], False)
+    g["display"], g["history"] = R.post_chain(color, normal, history, blend=0.1, jx=jx, jy=jy)
+    rng = np.random.default_rng(21)
+    g["equirect"] = (rng.random((32, 64, 3), dtype=np.float32) ** 4 * 60).astype(np.float32)
+    g["cube"] = R.equirect_to_cubemap(g["equirect"], 16)
+    np.savez_compressed(os.path.join(HERE, "post.npz"), **g)
+    print("wrote", len(g), "post arrays")
 
 
 if __name__ == "__main__":
