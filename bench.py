@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--stage", choices=["rt", "post"], default="rt",
+                    help="rt = the ray-tracing pass (the headline metric); post = the post chain (bench_post.py)")
     ap.add_argument("--config", type=int, default=2, help="BASELINE.json config number (1..5); the metric is quoted on 2")
     ap.add_argument("--width", type=int, default=None)
     ap.add_argument("--height", type=int, default=None)
@@ -417,6 +419,10 @@ def run_ours(args) -> None:
 
 def main():
     args = parse_args()
+    if args.stage == "post":
+        import bench_post
+        (bench_post.run_reference if args.impl == "reference" else bench_post.run_ours)(args)
+        return
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -19,6 +19,7 @@ struct PostState {
   void* bloom[2] = {nullptr, nullptr};   // bloomTextures[2], RGBA16F (src/ForwardShadingPipeline.cpp:67-84)
   size_t bloom_pixels = 0;
   uint64_t launches = 0;
+  bool pair_attr_set = false;            // opt-in shared memory size of blur_pair_kernel, per device
 };
 
 PostState* state_of(rt_context* c) {
@@ -208,6 +209,125 @@ __global__ void __launch_bounds__(256) blur_kernel(const uint2* __restrict__ in,
     r = mk(r.x + b.x * wi, r.y + b.y * wi, r.z + b.z * wi);
   }
   out[row + x] = pack_half_rgb1(r);
+}
+
+// ---------------------------------------------------------------- f3: fused blur pairs
+// One kernel = one horizontal + one vertical pass (the reference's passes 2k and 2k+1) over a
+// 64 x 56 output tile, optionally with the brightness extract fused in front (FIRST) and the bloom
+// combine behind (LAST). The intermediate image of the pair lives in shared memory as RGBA16F —
+// the same rounding the reference's RGBA16F render target applies — so the result is bit-identical
+// to the two separate passes while the pair reads its input once (1.29 x with the 4-texel halo)
+// and writes once. Both passes slide a 9-texel register window along the filter axis: one
+// shared-memory load and one conversion per tap-centre instead of nine.
+//   A: input region 72 x 64 texels (tile + 4 each side, coordinates clamped to the image: the
+//      CLAMP_TO_EDGE taps then simply read their neighbours), row stride 73 texels (odd: the H pass
+//      walks rows with one lane per row, conflict-free for 8-byte accesses)
+//   B: H-pass result 64 x 64, row stride 65
+constexpr int kPairW = 64, kPairH = 56, kPairR = 4;
+constexpr int kPairAW = kPairW + 2 * kPairR, kPairAH = kPairH + 2 * kPairR;      // 72 x 64
+constexpr int kPairAStride = kPairAW + 1, kPairBStride = kPairW + 1;
+constexpr int kPairSeg = 4;                                                       // 4 x 64 = 256 threads
+constexpr int kPairHRun = kPairW / kPairSeg, kPairVRun = kPairH / kPairSeg;        // 16, 14
+constexpr size_t kPairSmem = (size_t)(kPairAH * kPairAStride + kPairAH * kPairBStride) * sizeof(uint2);
+
+__device__ __forceinline__ f3 half_rgb(uint2 q) {
+  const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&q.x));
+  const float2 ba = __half22float2(*reinterpret_cast<const __half2*>(&q.y));
+  return mk(rg.x, rg.y, ba.x);
+}
+// centre, then (+i, -i) for i = 1..4: the shader's order. win[4] is the centre tap.
+__device__ __forceinline__ f3 blur9(const f3 (&win)[9]) {
+  f3 r = mk(win[4].x * c_blur_w[0], win[4].y * c_blur_w[0], win[4].z * c_blur_w[0]);
+#pragma unroll
+  for (int i = 1; i < 5; ++i) {
+    const float wi = c_blur_w[i];
+    r = mk(r.x + win[4 + i].x * wi, r.y + win[4 + i].y * wi, r.z + win[4 + i].z * wi);
+    r = mk(r.x + win[4 - i].x * wi, r.y + win[4 - i].y * wi, r.z + win[4 - i].z * wi);
+  }
+  return r;
+}
+
+template <bool FIRST, bool LAST>
+__global__ void __launch_bounds__(256, 3) blur_pair_kernel(const void* __restrict__ in, const float4* __restrict__ color,
+                                                        void* __restrict__ out, int w, int h, float threshold, float strength) {
+  extern __shared__ uint2 pair_smem[];
+  uint2* A = pair_smem;
+  uint2* B = pair_smem + kPairAH * kPairAStride;
+  const int x0 = blockIdx.x * kPairW, y0 = blockIdx.y * kPairH;
+  // ---- stage the input region (extract fused for the first pair): 18 texels per thread, loads
+  // issued in batches of 6 so that their latencies overlap
+  constexpr int kStageIters = kPairAW * kPairAH / 256, kStageBatch = 6;
+  static_assert(kPairAW * kPairAH % 256 == 0 && kStageIters % kStageBatch == 0, "staging loop shape");
+#pragma unroll 1
+  for (int it = 0; it < kStageIters; it += kStageBatch) {
+    float4 cq[kStageBatch];
+    uint2 hq[kStageBatch];
+#pragma unroll
+    for (int b = 0; b < kStageBatch; ++b) {
+      const int idx = (it + b) * 256 + threadIdx.x;
+      const int ry = idx / kPairAW, rx = idx - ry * kPairAW;
+      const size_t at = (size_t)clampi(y0 - kPairR + ry, 0, h - 1) * w + clampi(x0 - kPairR + rx, 0, w - 1);
+      if (FIRST) cq[b] = __ldg(static_cast<const float4*>(in) + at);
+      else hq[b] = __ldg(static_cast<const uint2*>(in) + at);
+    }
+#pragma unroll
+    for (int b = 0; b < kStageBatch; ++b) {
+      const int idx = (it + b) * 256 + threadIdx.x;
+      const int ry = idx / kPairAW, rx = idx - ry * kPairAW;
+      uint2 q;
+      if (FIRST) {
+        const f3 c = mk(cq[b].x, cq[b].y, cq[b].z);
+        const float brightness = (c.x * 0.2126f + c.y * 0.7152f) + c.z * 0.0722f;
+        q = pack_half_rgb1(brightness > threshold ? c : mk(0.0f, 0.0f, 0.0f));
+      } else {
+        q = hq[b];
+      }
+      A[ry * kPairAStride + rx] = q;
+    }
+  }
+  __syncthreads();
+  const int lane_item = threadIdx.x & 63, seg = threadIdx.x >> 6;
+  // ---- horizontal pass: one lane per row of A, a run of 16 outputs
+  {
+    const uint2* row = A + lane_item * kPairAStride + seg * kPairHRun;
+    uint2* dst = B + lane_item * kPairBStride + seg * kPairHRun;
+    f3 win[9];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) win[k + 1] = half_rgb(row[k]);
+#pragma unroll
+    for (int c = 0; c < kPairHRun; ++c) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) win[k] = win[k + 1];
+      win[8] = half_rgb(row[c + 8]);
+      dst[c] = pack_half_rgb1(blur9(win));
+    }
+  }
+  __syncthreads();
+  // ---- vertical pass: one lane per column of B, a run of 14 outputs
+  {
+    const int gx = x0 + lane_item;
+    const uint2* col = B + (seg * kPairVRun) * kPairBStride + lane_item;
+    f3 win[9];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) win[k + 1] = half_rgb(col[k * kPairBStride]);
+#pragma unroll
+    for (int r = 0; r < kPairVRun; ++r) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) win[k] = win[k + 1];
+      win[8] = half_rgb(col[(r + 8) * kPairBStride]);
+      const int gy = y0 + seg * kPairVRun + r;
+      const uint2 q = pack_half_rgb1(blur9(win));
+      if (gx < w && gy < h) {
+        const size_t at = (size_t)gy * w + gx;
+        if (LAST) {                                        // bloom_combineFs.glsl on the rounded result
+          const f3 s = ld_f32_rgb(color, at), b = half_rgb(q);
+          static_cast<float4*>(out)[at] = make_float4(s.x + b.x * strength, s.y + b.y * strength, s.z + b.z * strength, 1.0f);
+        } else {
+          static_cast<uint2*>(out)[at] = q;
+        }
+      }
+    }
+  }
 }
 
 // bloom_combineFs.glsl
@@ -419,6 +539,33 @@ rt_status rt_post_chain(rt_context* c, const rt_post_params* p, const float* d_c
     POST_CUDA(c, cudaMalloc(&ps->bloom[0], texels * 8));
     POST_CUDA(c, cudaMalloc(&ps->bloom[1], texels * 8));
     ps->bloom_pixels = texels;
+  }
+  if (!(p->flags & RT_POST_LITERAL_PASSES) && p->blur_passes >= 2 && (p->blur_passes & 1) == 0) {
+    // fused: extract + (H, V) pairs + combine, blur_passes / 2 launches
+    const int pairs = p->blur_passes / 2;
+    const dim3 grid((unsigned)((p->width + kPairW - 1) / kPairW), (unsigned)((p->height + kPairH - 1) / kPairH), 1);
+    const cudaStream_t s = (cudaStream_t)cuda_stream;
+    const float4* col = reinterpret_cast<const float4*>(d_color);
+    if (!ps->pair_attr_set) {
+      POST_CUDA(c, cudaFuncSetAttribute(blur_pair_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem));
+      POST_CUDA(c, cudaFuncSetAttribute(blur_pair_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem));
+      POST_CUDA(c, cudaFuncSetAttribute(blur_pair_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem));
+      POST_CUDA(c, cudaFuncSetAttribute(blur_pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem));
+      ps->pair_attr_set = true;
+    }
+    for (int k = 0; k < pairs; ++k) {
+      const bool first = k == 0, last = k == pairs - 1;
+      const void* in = first ? static_cast<const void*>(d_color) : ps->bloom[(k - 1) & 1];
+      void* out = last ? static_cast<void*>(d_display) : ps->bloom[k & 1];
+      if (first && last) blur_pair_kernel<true, true><<<grid, 256, kPairSmem, s>>>(in, col, out, p->width, p->height, p->bloom_threshold, p->bloom_strength);
+      else if (first) blur_pair_kernel<true, false><<<grid, 256, kPairSmem, s>>>(in, col, out, p->width, p->height, p->bloom_threshold, p->bloom_strength);
+      else if (last) blur_pair_kernel<false, true><<<grid, 256, kPairSmem, s>>>(in, col, out, p->width, p->height, p->bloom_threshold, p->bloom_strength);
+      else blur_pair_kernel<false, false><<<grid, 256, kPairSmem, s>>>(in, col, out, p->width, p->height, p->bloom_threshold, p->bloom_strength);
+      st = launched(c, "rt_post_chain (blur pair)");
+      if (st != RT_OK) return st;
+    }
+    if (p->taa_enabled) st = rt_taa_resolve(c, p, d_color, d_history_prev, d_normal, d_history_out, cuda_stream);
+    return st;
   }
   st = rt_bloom_extract(c, p, d_color, ps->bloom[0], cuda_stream);                          // :192-201
   if (st != RT_OK) return st;
