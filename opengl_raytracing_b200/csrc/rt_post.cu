@@ -20,6 +20,8 @@ struct PostState {
   size_t bloom_pixels = 0;
   uint64_t launches = 0;
   bool pair_attr_set = false;            // opt-in shared memory size of blur_pair_kernel, per device
+  cudaStream_t aux = nullptr;            // TAA runs beside the bloom pairs (both only read the colour image)
+  cudaEvent_t fork = nullptr, join = nullptr;
 };
 
 PostState* state_of(rt_context* c) {
@@ -43,6 +45,11 @@ __device__ __forceinline__ f3 mk(float x, float y, float z) { f3 v; v.x = x; v.y
 // RGBA16F texel -> rgb as FP32 (exact)
 __device__ __forceinline__ f3 ld_half_rgb(const uint2* img, size_t at) {
   const uint2 q = __ldg(img + at);
+  const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&q.x));
+  const float2 ba = __half22float2(*reinterpret_cast<const __half2*>(&q.y));
+  return mk(rg.x, rg.y, ba.x);
+}
+__device__ __forceinline__ f3 half_rgb(uint2 q) {
   const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&q.x));
   const float2 ba = __half22float2(*reinterpret_cast<const __half2*>(&q.y));
   return mk(rg.x, rg.y, ba.x);
@@ -74,7 +81,10 @@ __device__ __forceinline__ float lerp_tap(float t0, float t1, float a) {
   return t0 * (1.0f - a) + t1 * a;
 }
 __device__ __forceinline__ f3 lerp_tap(f3 t0, f3 t1, float a) {
-  return mk(lerp_tap(t0.x, t1.x, a), lerp_tap(t0.y, t1.y, a), lerp_tap(t0.z, t1.z, a));
+  if (a == 0.0f) return t0;
+  if (a == 1.0f) return t1;
+  const float ia = 1.0f - a;
+  return mk(t0.x * ia + t1.x * a, t0.y * ia + t1.y * a, t0.z * ia + t1.z * a);
 }
 
 // ---------------------------------------------------------------- f1: AABBs
@@ -230,11 +240,6 @@ constexpr int kPairSeg = 4;                                                     
 constexpr int kPairHRun = kPairW / kPairSeg, kPairVRun = kPairH / kPairSeg;        // 16, 14
 constexpr size_t kPairSmem = (size_t)(kPairAH * kPairAStride + kPairAH * kPairBStride) * sizeof(uint2);
 
-__device__ __forceinline__ f3 half_rgb(uint2 q) {
-  const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&q.x));
-  const float2 ba = __half22float2(*reinterpret_cast<const __half2*>(&q.y));
-  return mk(rg.x, rg.y, ba.x);
-}
 // centre, then (+i, -i) for i = 1..4: the shader's order. win[4] is the centre tap.
 __device__ __forceinline__ f3 blur9(const f3 (&win)[9]) {
   f3 r = mk(win[4].x * c_blur_w[0], win[4].y * c_blur_w[0], win[4].z * c_blur_w[0]);
@@ -254,35 +259,40 @@ __global__ void __launch_bounds__(256, 3) blur_pair_kernel(const void* __restric
   uint2* A = pair_smem;
   uint2* B = pair_smem + kPairAH * kPairAStride;
   const int x0 = blockIdx.x * kPairW, y0 = blockIdx.y * kPairH;
-  // ---- stage the input region (extract fused for the first pair): 18 texels per thread, loads
-  // issued in batches of 6 so that their latencies overlap
+  // ---- stage the input region: 18 texels per thread. Later pairs copy RGBA16F texels straight
+  // into shared memory with cp.async (all 18 in flight at once, no registers); the first pair
+  // converts RGBA32F colour through the brightness extract, in register batches of 6.
   constexpr int kStageIters = kPairAW * kPairAH / 256, kStageBatch = 6;
   static_assert(kPairAW * kPairAH % 256 == 0 && kStageIters % kStageBatch == 0, "staging loop shape");
-#pragma unroll 1
-  for (int it = 0; it < kStageIters; it += kStageBatch) {
-    float4 cq[kStageBatch];
-    uint2 hq[kStageBatch];
+  if (!FIRST) {
 #pragma unroll
-    for (int b = 0; b < kStageBatch; ++b) {
-      const int idx = (it + b) * 256 + threadIdx.x;
+    for (int it = 0; it < kStageIters; ++it) {
+      const int idx = it * 256 + threadIdx.x;
       const int ry = idx / kPairAW, rx = idx - ry * kPairAW;
       const size_t at = (size_t)clampi(y0 - kPairR + ry, 0, h - 1) * w + clampi(x0 - kPairR + rx, 0, w - 1);
-      if (FIRST) cq[b] = __ldg(static_cast<const float4*>(in) + at);
-      else hq[b] = __ldg(static_cast<const uint2*>(in) + at);
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(A + ry * kPairAStride + rx);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(static_cast<const uint2*>(in) + at) : "memory");
     }
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+  } else {
+#pragma unroll 1
+    for (int it = 0; it < kStageIters; it += kStageBatch) {
+      float4 cq[kStageBatch];
 #pragma unroll
-    for (int b = 0; b < kStageBatch; ++b) {
-      const int idx = (it + b) * 256 + threadIdx.x;
-      const int ry = idx / kPairAW, rx = idx - ry * kPairAW;
-      uint2 q;
-      if (FIRST) {
+      for (int b = 0; b < kStageBatch; ++b) {
+        const int idx = (it + b) * 256 + threadIdx.x;
+        const int ry = idx / kPairAW, rx = idx - ry * kPairAW;
+        const size_t at = (size_t)clampi(y0 - kPairR + ry, 0, h - 1) * w + clampi(x0 - kPairR + rx, 0, w - 1);
+        cq[b] = __ldg(static_cast<const float4*>(in) + at);
+      }
+#pragma unroll
+      for (int b = 0; b < kStageBatch; ++b) {
+        const int idx = (it + b) * 256 + threadIdx.x;
+        const int ry = idx / kPairAW, rx = idx - ry * kPairAW;
         const f3 c = mk(cq[b].x, cq[b].y, cq[b].z);
         const float brightness = (c.x * 0.2126f + c.y * 0.7152f) + c.z * 0.0722f;
-        q = pack_half_rgb1(brightness > threshold ? c : mk(0.0f, 0.0f, 0.0f));
-      } else {
-        q = hq[b];
+        A[ry * kPairAStride + rx] = pack_half_rgb1(brightness > threshold ? c : mk(0.0f, 0.0f, 0.0f));
       }
-      A[ry * kPairAStride + rx] = q;
     }
   }
   __syncthreads();
@@ -345,41 +355,81 @@ __device__ __forceinline__ f3 fetch_or_zero(const float4* img, int w, int h, int
   return ld_f32_rgb(img, (size_t)y * w + x);
 }
 
+// wrap for coordinates that are almost always already inside [0, n)
+__device__ __forceinline__ int wrap_fast(int i, int n) { return ((unsigned)i < (unsigned)n) ? i : wrap_repeat(i, n); }
+
+// block (32, 8): the 34 x 10 colour texels around the block are staged in shared memory once
+// (zeros outside the image: the texelFetch rule above), so the 3x3 neighbourhood and — when the
+// jitter keeps them inside the staged region, the normal case — the four bilinear texels cost no
+// further global loads. Per thread: ~1.3 colour + history + 2 normal loads.
+constexpr int kTaaW = 32, kTaaH = 8, kTaaTW = kTaaW + 2, kTaaTH = kTaaH + 2;
 __global__ void __launch_bounds__(256) taa_kernel(const float4* __restrict__ color, const float4* __restrict__ history,
                                                   const uint2* __restrict__ normal, float4* __restrict__ out, int w, int h,
                                                   float blend_factor, float jx, float jy) {
-  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
-  if (x >= w || y >= h) return;
+  __shared__ float4 tile[kTaaTH * kTaaTW];
+  const int x0 = blockIdx.x * kTaaW, y0 = blockIdx.y * kTaaH;
+  const int tid = threadIdx.y * kTaaW + threadIdx.x;
+  for (int idx = tid; idx < kTaaTW * kTaaTH; idx += 256) {
+    const int ty = idx / kTaaTW, tx = idx - ty * kTaaTW;
+    const int gx = x0 - 1 + tx, gy = y0 - 1 + ty;
+    float4 q = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (gx >= 0 && gy >= 0 && gx < w && gy < h) q = __ldg(color + (size_t)gy * w + gx);
+    tile[idx] = q;
+  }
+  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+  const bool inside = x < w && y < h;
+  const size_t at = (size_t)y * w + x;
+  float4 hq = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  uint2 nq = make_uint2(0u, 0u), nq2 = make_uint2(0u, 0u);
   const float W = (float)w, H = (float)h;
   const float tu = ((float)x + 0.5f) / W, tv = ((float)y + 0.5f) / H;           // TexCoords
   const float ju = tu + jx, jv = tv + jy;                                       // jitteredUV
-  // current: GL_LINEAR, REPEAT
+  if (inside) {                                                                 // issue the independent loads before the barrier
+    hq = __ldg(history + at);
+    nq = __ldg(normal + at);
+    const int nx = wrap_fast((int)floorf(ju * W), w), ny = wrap_fast((int)floorf(jv * H), h);   // GL_NEAREST, REPEAT
+    nq2 = __ldg(normal + (size_t)ny * w + nx);
+  }
+  __syncthreads();
+  if (!inside) return;
+  // current: GL_LINEAR, REPEAT. The four texels come from the staged region when all of them are
+  // inside it (any jitter below one texel), else from global memory.
   f3 current;
   {
     const float u = ju * W - 0.5f, v = jv * H - 0.5f;
     const float fu = floorf(u), fv = floorf(v);
     const float a = snap_weight(u - fu), b = snap_weight(v - fv);
-    const int i0 = wrap_repeat((int)fu, w), i1 = wrap_repeat((int)fu + 1, w);
-    const int j0 = wrap_repeat((int)fv, h), j1 = wrap_repeat((int)fv + 1, h);
-    const f3 top = lerp_tap(ld_f32_rgb(color, (size_t)j0 * w + i0), ld_f32_rgb(color, (size_t)j0 * w + i1), a);
-    const f3 bot = lerp_tap(ld_f32_rgb(color, (size_t)j1 * w + i0), ld_f32_rgb(color, (size_t)j1 * w + i1), a);
-    current = lerp_tap(top, bot, b);
-  }
-  f3 hist = ld_f32_rgb(history, (size_t)y * w + x);
-  f3 lo = current, hi = current;
-#pragma unroll
-  for (int dx = -1; dx <= 1; ++dx)
-#pragma unroll
-    for (int dy = -1; dy <= 1; ++dy) {
-      const f3 nb = fetch_or_zero(color, w, h, x + dx, y + dy);
-      lo = min3v(lo, nb);
-      hi = max3v(hi, nb);
+    const int i0 = wrap_fast((int)fu, w), i1 = wrap_fast((int)fu + 1, w);
+    const int j0 = wrap_fast((int)fv, h), j1 = wrap_fast((int)fv + 1, h);
+    const int ti0 = i0 - x0 + 1, ti1 = i1 - x0 + 1, tj0 = j0 - y0 + 1, tj1 = j1 - y0 + 1;
+    f3 t00, t10, t01, t11;
+    if ((unsigned)ti0 < (unsigned)kTaaTW && (unsigned)ti1 < (unsigned)kTaaTW && (unsigned)tj0 < (unsigned)kTaaTH && (unsigned)tj1 < (unsigned)kTaaTH) {
+      const float4 q00 = tile[tj0 * kTaaTW + ti0], q10 = tile[tj0 * kTaaTW + ti1];
+      const float4 q01 = tile[tj1 * kTaaTW + ti0], q11 = tile[tj1 * kTaaTW + ti1];
+      t00 = mk(q00.x, q00.y, q00.z); t10 = mk(q10.x, q10.y, q10.z); t01 = mk(q01.x, q01.y, q01.z); t11 = mk(q11.x, q11.y, q11.z);
+    } else {
+      t00 = ld_f32_rgb(color, (size_t)j0 * w + i0); t10 = ld_f32_rgb(color, (size_t)j0 * w + i1);
+      t01 = ld_f32_rgb(color, (size_t)j1 * w + i0); t11 = ld_f32_rgb(color, (size_t)j1 * w + i1);
     }
+    current = lerp_tap(lerp_tap(t00, t10, a), lerp_tap(t01, t11, a), b);
+  }
+  f3 hist = mk(hq.x, hq.y, hq.z);
+  f3 lo = current, hi = current;
+  {
+    const float4* t0 = tile + threadIdx.y * kTaaTW + threadIdx.x;               // tile coords of (x - 1, y - 1)
+#pragma unroll
+    for (int dx = 0; dx < 3; ++dx)                                              // the shader's order: x outer, y inner
+#pragma unroll
+      for (int dy = 0; dy < 3; ++dy) {
+        const float4 q = t0[dy * kTaaTW + dx];
+        const f3 nb = mk(q.x, q.y, q.z);
+        lo = min3v(lo, nb);
+        hi = max3v(hi, nb);
+      }
+  }
   float blend = 0.0f;
   {
-    const f3 prev = ld_half_rgb(normal, (size_t)y * w + x);
-    const int nx = wrap_repeat((int)floorf(ju * W), w), ny = wrap_repeat((int)floorf(jv * H), h);   // GL_NEAREST, REPEAT
-    const f3 curr = ld_half_rgb(normal, (size_t)ny * w + nx);
+    const f3 prev = half_rgb(nq), curr = half_rgb(nq2);
     if ((prev.x * curr.x + prev.y * curr.y) + prev.z * curr.z < 0.9f) blend = blend_factor * 0.2f;
   }
   // clipAABB
@@ -389,8 +439,7 @@ __global__ void __launch_bounds__(256) taa_kernel(const float4* __restrict__ col
   clip = mk(fminf(fmaxf(clip.x, -ext.x), ext.x), fminf(fmaxf(clip.y, -ext.y), ext.y), fminf(fmaxf(clip.z, -ext.z), ext.z));
   hist = mk(center.x + clip.x, center.y + clip.y, center.z + clip.z);
   const float ia = 1.0f - blend;
-  out[(size_t)y * w + x] = make_float4(hist.x * ia + current.x * blend, hist.y * ia + current.y * blend,
-                                       hist.z * ia + current.z * blend, 1.0f);
+  out[at] = make_float4(hist.x * ia + current.x * blend, hist.y * ia + current.y * blend, hist.z * ia + current.z * blend, 1.0f);
 }
 
 }  // namespace rt_post
@@ -403,6 +452,9 @@ void post_release(void* state) {
   if (!st) return;
   cudaFree(st->bloom[0]);
   cudaFree(st->bloom[1]);
+  if (st->fork) cudaEventDestroy(st->fork);
+  if (st->join) cudaEventDestroy(st->join);
+  if (st->aux) cudaStreamDestroy(st->aux);
   delete st;
 }
 }  // namespace rt
@@ -553,6 +605,18 @@ rt_status rt_post_chain(rt_context* c, const rt_post_params* p, const float* d_c
       POST_CUDA(c, cudaFuncSetAttribute(blur_pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmem));
       ps->pair_attr_set = true;
     }
+    if (p->taa_enabled) {                                  // fork: TAA on the auxiliary stream
+      if (!ps->aux) {
+        POST_CUDA(c, cudaStreamCreateWithFlags(&ps->aux, cudaStreamNonBlocking));
+        POST_CUDA(c, cudaEventCreateWithFlags(&ps->fork, cudaEventDisableTiming));
+        POST_CUDA(c, cudaEventCreateWithFlags(&ps->join, cudaEventDisableTiming));
+      }
+      POST_CUDA(c, cudaEventRecord(ps->fork, s));
+      POST_CUDA(c, cudaStreamWaitEvent(ps->aux, ps->fork, 0));
+      st = rt_taa_resolve(c, p, d_color, d_history_prev, d_normal, d_history_out, ps->aux);
+      if (st != RT_OK) return st;
+      POST_CUDA(c, cudaEventRecord(ps->join, ps->aux));
+    }
     for (int k = 0; k < pairs; ++k) {
       const bool first = k == 0, last = k == pairs - 1;
       const void* in = first ? static_cast<const void*>(d_color) : ps->bloom[(k - 1) & 1];
@@ -564,7 +628,7 @@ rt_status rt_post_chain(rt_context* c, const rt_post_params* p, const float* d_c
       st = launched(c, "rt_post_chain (blur pair)");
       if (st != RT_OK) return st;
     }
-    if (p->taa_enabled) st = rt_taa_resolve(c, p, d_color, d_history_prev, d_normal, d_history_out, cuda_stream);
+    if (p->taa_enabled) POST_CUDA(c, cudaStreamWaitEvent(s, ps->join, 0));   // join
     return st;
   }
   st = rt_bloom_extract(c, p, d_color, ps->bloom[0], cuda_stream);                          // :192-201
