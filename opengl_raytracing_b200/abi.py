@@ -36,6 +36,10 @@ EXPORTED_SYMBOLS = [
     "rt_get_counters", "rt_set_host_path", "rt_device_alloc", "rt_device_free", "rt_ipc_export",
     "rt_ipc_open", "rt_ipc_close", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
 ]
+POST_EXPORTED_SYMBOLS = [                   # include/rt_post.h
+    "rt_generate_aabbs", "rt_generate_aabbs_device", "rt_decode_rgbe", "rt_equirect_to_cubemap",
+    "rt_bloom_extract", "rt_gaussian_blur", "rt_bloom_combine", "rt_taa_resolve", "rt_post_chain", "rt_post_launch_count",
+]
 
 
 class RtLibraryError(RuntimeError):

@@ -1,4 +1,4 @@
-"""C-ABI library: loads and exports every symbol include/rt_abi.h declares; the ctypes
+"""C-ABI library: loads and exports every symbol include/rt_abi.h and include/rt_post.h declare; the ctypes
 structures match the header's byte layouts. No compute calls (runs without a GPU)."""
 import ctypes as C
 import os
@@ -12,10 +12,11 @@ from opengl_raytracing_b200 import abi, scene as S
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "rt_abi.h")
+POST_HEADER = os.path.join(ROOT, "include", "rt_post.h")
 
 
-def _declared_functions():
-    text = open(HEADER).read()
+def _declared_functions(header=HEADER):
+    text = open(header).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     names = re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", text)
     return sorted(set(names))
@@ -23,13 +24,14 @@ def _declared_functions():
 
 def test_header_functions_match_binding_list():
     assert _declared_functions() == sorted(abi.EXPORTED_SYMBOLS)
+    assert _declared_functions(POST_HEADER) == sorted(abi.POST_EXPORTED_SYMBOLS)
 
 
 def test_library_loads_and_exports_every_symbol():
     from opengl_raytracing_b200 import build
     build.build()
     lib = abi.load_library()
-    for name in _declared_functions():
+    for name in _declared_functions() + _declared_functions(POST_HEADER):
         assert hasattr(lib, name), name
     assert lib.rt_abi_version() == 2
     assert lib.rt_status_string(5) == b"RT_ERR_UNAVAILABLE"
@@ -56,6 +58,17 @@ def test_struct_layouts_against_c_compiler(tmp_path):
     assert int(out["sizeof.rt_light"]) == 96 == S.LIGHT_DTYPE.itemsize
     assert int(out["sizeof.rt_aabb"]) == 32 == S.AABB_DTYPE.itemsize
     assert int(out["sizeof.rt_frame_params"]) == C.sizeof(abi.FrameParams)
+    # rt_post_params
+    psrc = tmp_path / "probe_post.c"
+    pf = ("width", "height", "bloom_threshold", "bloom_strength", "blur_passes", "taa_enabled", "taa_blend", "jitter_x", "jitter_y", "flags")
+    pbody = "".join(f'printf("{f} %zu\\n", offsetof(rt_post_params, {f}));\n' for f in pf) + 'printf("sizeof %zu\\n", sizeof(rt_post_params));\n'
+    psrc.write_text(f'#include <stdio.h>\n#include "{POST_HEADER}"\nint main(void){{\n{pbody}return 0;}}\n')
+    pexe = tmp_path / "probe_post"
+    subprocess.run(["gcc", "-std=c11", str(psrc), "-o", str(pexe)], check=True)
+    pout = dict(l.split() for l in subprocess.run([str(pexe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    assert int(pout["sizeof"]) == C.sizeof(abi.PostParams)
+    for f in pf:
+        assert getattr(abi.PostParams, f).offset == int(pout[f]), f
     for dt, name in ((S.OBJECT_DTYPE, "rt_object"), (S.MATERIAL_DTYPE, "rt_material"), (S.LIGHT_DTYPE, "rt_light")):
         for f in dt.names:
             key = f"{name}.{f}"
