@@ -50,9 +50,18 @@ __device__ __forceinline__ float sqrt_shade(float x) { return __fsqrt_rn(x); }
 __device__ __forceinline__ float inversesqrt_shade(float x) { return __frcp_rn(__fsqrt_rn(x)); }
 __device__ __forceinline__ float pow5(float x) { return powf(x, 5.0f); }
 #else
+// Colour-only sites: single MUFU forms (.ftz: no denormal-range fix-up sequence; a denormal
+// operand or result is a colour term below 1.2e-38). Measured on C2: -4 % kernel time for the
+// shadow-ray pair of these alone (profiles/README.md).
+#if RT_PK_NO_FTZ
 __device__ __forceinline__ float div_shade(float a, float b) { return __fdividef(a, b); }
 __device__ __forceinline__ float sqrt_shade(float x) { return sqrtf(x); }
 __device__ __forceinline__ float inversesqrt_shade(float x) { return rsqrtf(x); }
+#else
+__device__ __forceinline__ float div_shade(float a, float b) { float r; asm("div.approx.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float sqrt_shade(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float inversesqrt_shade(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#endif
 __device__ __forceinline__ float pow5(float x) { float x2 = x * x; return x2 * x2 * x; }
 #endif
 __device__ __forceinline__ float pow2(float x) { return x * x; }                       // pow(x, 2.0)
