@@ -288,7 +288,13 @@ template <bool BIG>
 __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3 o, f3 d) {
   const f3 inv = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
   const float a = dot3(d, d);
-  if (!dir_regular(d, a)) return trace_closest_generic(s, o, d, inv, a);
+  if (!dir_regular(d, a)) {
+    // rare path: the out-of-line routine takes COPIES, so that the structs of the common path are
+    // never address-taken and stay in registers (a by-reference argument of a noinline function
+    // pins its object in local memory: measured 6 % of the kernel's instructions as STL/LDL)
+    const Scene s2 = s;
+    return trace_closest_generic(s2, o, d, inv, a);
+  }
   return trace_one<false, BIG>(s, cand_base, o, d, inv, a);
 }
 
@@ -431,7 +437,10 @@ __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands
     ivx[r] = dup2(rcp_shadow(d[r].x)); ivy[r] = dup2(rcp_shadow(d[r].y)); ivz[r] = dup2(rcp_shadow(d[r].z));   // FMUL2 takes the scalar broadcast form
     if (((active >> r) & 1u) && !dir_regular(d[r], a[r])) {
       remaining &= ~(1u << r);
-      if (a[r] == a[r] && trace_any_one(s, cd, cone, o, d[r], lim)) occ |= 1u << r;     // a is NaN iff a component is
+      if (a[r] == a[r]) {                                                               // a is NaN iff a component is
+        const Scene s2 = s; const Cands cd2 = cd; const Cone cone2 = cone;              // copies: see trace_closest
+        if (trace_any_one(s2, cd2, cone2, o, d[r], lim)) occ |= 1u << r;
+      }
     }
   }
   const float nox = -o.x, noy = -o.y, noz = -o.z;
@@ -643,7 +652,10 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     else if (sampled) shadowFactor = shadow_packets<BIG>(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
     Lo = Lo + brdf * shadowFactor;
   }
-  if (lit && mat.subsurfaceScatter > 0.0f) Lo = Lo + subsurface(s, P, N, mat);
+  if (lit && mat.subsurfaceScatter > 0.0f) {
+    const Scene s2 = s; const Mat mat2 = mat;                                           // copies: see trace_closest
+    Lo = Lo + subsurface(s2, P, N, mat2);
+  }
   return Lo;
 }
 
