@@ -194,7 +194,7 @@ def run_reference(args) -> None:
         "e2e": {"value": val, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args) -> None:
@@ -221,8 +221,7 @@ def run_ours(args) -> None:
                 os.sched_setaffinity(0, cpus)
         except Exception:
             pass
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # (stdout is guarded as well: guard_stdout)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     w = workload_for(args)
@@ -407,7 +406,7 @@ def run_ours(args) -> None:
             kind = "reference" if oracle.have("reference") else "port"
             cb = cpu_baseline(w, kind, budget_s=12.0, step=args.cpu_sample_step)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if peer:
         torch.cuda.synchronize(dev)
         dist.barrier()
@@ -417,11 +416,32 @@ def run_ours(args) -> None:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def guard_stdout() -> None:
+    """stdout carries exactly ONE line — the JSON result. Libraries loaded below (NCCL's version
+    banner, torch.distributed notices) write to file descriptor 1 on their own: point fd 1 at
+    stderr for the duration of the run and keep the real stdout for emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
     args = parse_args()
+    guard_stdout()
     if args.stage == "post":
         import bench_post
-        (bench_post.run_reference if args.impl == "reference" else bench_post.run_ours)(args)
+        (bench_post.run_reference if args.impl == "reference" else bench_post.run_ours)(args, emit)
         return
     if args.impl == "reference":
         run_reference(args)

@@ -44,7 +44,7 @@ def _oracle_kind():
     return "reference" if oracle.have_post("reference") else "port"
 
 
-def run_reference(args) -> None:
+def run_reference(args, emit) -> None:
     import numpy as np
     if int(os.environ.get("RANK", "0")) != 0:
         return
@@ -73,10 +73,10 @@ def run_reference(args) -> None:
             "cpu_baseline": {"value": v, "unit": METRIC, "cores": cores, "kind": kind,
                              "sample": f"full {W}x{H} frame, OpenMP static over rows, {steps} steps"},
             "e2e": {"value": v, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
-def run_ours(args) -> None:
+def run_ours(args, emit) -> None:
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -91,8 +91,7 @@ def run_ours(args) -> None:
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     ctx = RtContext(local)
@@ -207,7 +206,7 @@ def run_ours(args) -> None:
             dt = _cpu(kind, k["color"], k["normal"], hist_np, jx0, jy0, repeats=2)
             line["cpu_baseline"] = {"value": px / dt / 1e6, "unit": METRIC, "cores": os.cpu_count(), "kind": kind,
                                     "sample": f"full {W}x{H} frame, best of 2, OpenMP static over rows"}
-        print(json.dumps(line))
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
