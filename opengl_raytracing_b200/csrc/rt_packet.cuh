@@ -608,7 +608,29 @@ __device__ __noinline__ f3 subsurface(const Scene& s, f3 P, f3 N, const Mat& mat
 
 // Phase barrier of the CTA-coherent mode (see the kernel): keeps the warps that share an SM
 // sub-partition inside the same stretch of code. `coh` is kernel-uniform.
-__device__ __forceinline__ void phase_sync(bool on) { if (on) __syncthreads(); }
+// RT_PK_SYNC_WARPS (dev A/B): phase barriers over groups of that many warps (named barriers
+// 1 + warp / group) instead of the whole CTA.
+#ifndef RT_PK_SYNC_WARPS
+#define RT_PK_SYNC_WARPS 0
+#endif
+__device__ __forceinline__ void phase_sync(bool on) {
+  if (!on) return;
+#if RT_PK_SYNC_WARPS > 0
+  asm volatile("bar.sync %0, %1;" ::"r"(1u + (threadIdx.x >> 5) / RT_PK_SYNC_WARPS), "r"(32u * RT_PK_SYNC_WARPS) : "memory");
+#else
+  __syncthreads();
+#endif
+}
+__device__ __forceinline__ bool phase_any(bool pred) {
+#if RT_PK_SYNC_WARPS > 0
+  unsigned r;
+  asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %3, 0;\n\tbar.red.or.pred p, %1, %2, q;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(r) : "r"(1u + (threadIdx.x >> 5) / RT_PK_SYNC_WARPS), "r"(32u * RT_PK_SYNC_WARPS), "r"((unsigned)pred) : "memory");
+  return r != 0u;
+#else
+  return __syncthreads_or(pred) != 0;
+#endif
+}
 
 // computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
 // lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
@@ -694,7 +716,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 
 #pragma unroll 1
   for (int depth = 0; depth < fp.max_ray_depth; ++depth) {
-    if (!(coh >= 2 ? __syncthreads_or(alive) : __any_sync(0xffffffffu, alive))) break;
+    if (!(coh >= 2 ? phase_any(alive) : __any_sync(0xffffffffu, alive) != 0u)) break;
     bool lit = false;
     f3 N = mk3(0.0f, 0.0f, 0.0f), P = N, V = N;
     Mat mat = {};
