@@ -782,8 +782,13 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 // BANDS = true: interleaved row bands (rt_frame_params.row_band > 0). A separate instantiation
 // because the register allocation of the whole kernel moves with this one expression (measured
 // on C2: 0.571 ms without the band arithmetic compiled in, 0.626 ms with it).
-template <bool BIG, bool BANDS>
-__global__ void __launch_bounds__(kThreads, RT_PK_MINBLOCKS * 8 / RT_PK_WARPS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
+// MINB = resident CTAs per SM the register budget is sized for: 2 (128 registers, 16 warps) or, for
+// the large-scene kernel, also 3 (80 registers, 24 warps, more spills). Same source, same
+// arithmetic (-fmad=false: nothing contracts differently), bit-identical images; which one is
+// faster depends on the scene (B200: C3 39.5 -> 35.1 ms with 3, C5 10.9 -> 12.0 ms), so the host
+// times both on the first frames of a scene and keeps the faster (rt_abi.cu).
+template <bool BIG, bool BANDS, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB * 8 / RT_PK_WARPS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const DeviceScene& sc = kp.sc;
   const rt_frame_params& fp = kp.fp;
@@ -888,13 +893,13 @@ inline cudaError_t upload_probe_order(const float* halton3, const int* order16) 
   return cudaMemcpyToSymbol(c_probe_rv, rv, sizeof(rv));
 }
 
-template <bool BIG, bool BANDS>
+template <bool BIG, bool BANDS, int MINB>
 inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
-  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel<BIG, BANDS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel<BIG, BANDS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel<BIG, BANDS>, kThreads, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel<BIG, BANDS, MINB>, kThreads, smem);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
@@ -907,17 +912,21 @@ inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStr
   // tile + one failing fetch per warp; coherent mode = one per block + one per CTA.
   if (!BIG && kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
   else *warps_launched = ctas * kWarpsPerCta;
-  rt_packet_kernel<BIG, BANDS><<<ctas, kThreads, smem, stream>>>(kp);
+  rt_packet_kernel<BIG, BANDS, MINB><<<ctas, kThreads, smem, stream>>>(kp);
   return cudaGetLastError();
 }
 
 // kp.sc.pk_big (host-chosen by object count) selects the kernel.
 inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
-  if (kp.fp.row_band > 0)
-    return kp.sc.pk_big ? launch_packet_t<true, true>(kp, sm_count, stream, warps_launched)
-                        : launch_packet_t<false, true>(kp, sm_count, stream, warps_launched);
-  return kp.sc.pk_big ? launch_packet_t<true, false>(kp, sm_count, stream, warps_launched)
-                      : launch_packet_t<false, false>(kp, sm_count, stream, warps_launched);
+  constexpr int kMinB = RT_PK_MINBLOCKS;
+  if (kp.fp.row_band > 0) {
+    if (!kp.sc.pk_big) return launch_packet_t<false, true, kMinB>(kp, sm_count, stream, warps_launched);
+    return kp.sc.pk_dense ? launch_packet_t<true, true, 3>(kp, sm_count, stream, warps_launched)
+                          : launch_packet_t<true, true, kMinB>(kp, sm_count, stream, warps_launched);
+  }
+  if (!kp.sc.pk_big) return launch_packet_t<false, false, kMinB>(kp, sm_count, stream, warps_launched);
+  return kp.sc.pk_dense ? launch_packet_t<true, false, 3>(kp, sm_count, stream, warps_launched)
+                        : launch_packet_t<true, false, kMinB>(kp, sm_count, stream, warps_launched);
 }
 
 }  // namespace pk
