@@ -1,7 +1,7 @@
 """Dev helper (GPU box): parity of every config at small sizes, both kernel variants."""
 import sys, time, json
 import numpy as np
-sys.path.insert(0, "tests")
+sys.path.insert(0, "tests"); sys.path.insert(0, ".")
 import oracle
 from parity import compare
 from opengl_raytracing_b200 import synthetic, abi
