@@ -58,6 +58,8 @@ def parse_args():
     ap.add_argument("--stage", choices=["rt", "post"], default="rt",
                     help="rt = the ray-tracing pass (the headline metric); post = the post chain (bench_post.py)")
     ap.add_argument("--config", type=int, default=2, help="BASELINE.json config number (1..5); the metric is quoted on 2")
+    ap.add_argument("--scene", choices=["default", "SIMPLE", "performance_test"], default=None,
+                    help="a shipped scene file of the reference instead of a BASELINE config (1920x1080, depth 3)")
     ap.add_argument("--width", type=int, default=None)
     ap.add_argument("--height", type=int, default=None)
     ap.add_argument("--samples", type=int, default=None, help="override num_samples (config 4 defaults to 64)")
@@ -74,6 +76,21 @@ def parse_args():
 
 def workload_for(args):
     from opengl_raytracing_b200 import synthetic
+    if args.scene:
+        # one of the reference's shipped scene files (res/Scene/*.scene), from the decoded bytes
+        # committed under tests/golden (the reference tree does not exist on the GPU box), as the
+        # reference would show it at start-up: Camera defaults, light defaults (PCF x4), depth 3
+        import numpy as np
+        from opengl_raytracing_b200 import scene as S
+        g = np.load(os.path.join(ROOT, "tests", "golden", "scenes.npz"))
+        objs = g[args.scene + "_objects"].copy().view(S.OBJECT_DTYPE)
+        lights = g[args.scene + "_lights"].copy().view(S.LIGHT_DTYPE)
+        w = synthetic.Workload(args.scene, objs, lights, args.width or 1920, args.height or 1080, 3, use_skybox=True,
+                               skybox=synthetic.skybox_s1(), noise=synthetic.noise_n1(),
+                               description=f"res/Scene/{args.scene}.scene ({len(objs)} objects, {len(lights)} lights), Camera defaults, skybox S1, noise N1, depth 3, 1 spp")
+        if args.samples is not None:
+            w.num_samples = args.samples
+        return w
     w = synthetic.config(args.config, args.width, args.height)
     if args.samples is not None:
         w.num_samples = args.samples

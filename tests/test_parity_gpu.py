@@ -273,6 +273,22 @@ def test_full_size_pixel_subset(rt_ctx, port_oracle, n):
     assert_parity(st)
 
 
+@pytest.mark.parametrize("name", ["performance_test", "SIMPLE"])
+def test_shipped_scenes_at_1080p_pixel_subset(rt_ctx, port_oracle, name):
+    """The reference's own scene files (15 objects, 8 / 3 lights, short-line glass spheres with
+    ior = 0) at 1920x1080 with skybox and noise bound: kernel frame vs the oracle on the 1/64 subset."""
+    from edge_cases import shipped_scene
+    w = shipped_scene(name, (1920, 1080), 3)
+    w.use_skybox, w.skybox, w.noise = True, synthetic.skybox_s1(), synthetic.noise_n1()
+    o = port_oracle.render(w, "port", x0=3, y0=5, sx=8, sy=8)
+    k = render_workload(rt_ctx, w, flags=0)
+    sub = {key: v[5::8, 3::8] for key, v in k.items()}
+    assert_parity(compare(sub, o, normal_fp16=True))
+    a = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32, bind=False)
+    b = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32 | abi.FLAG_LITERAL_KERNEL, bind=False)
+    assert _bits_equal(a, b) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
+
+
 def test_errors_are_status_codes(rt_ctx):
     w = synthetic.config(1, 32, 18)
     bind_workload(rt_ctx, w)

@@ -1,4 +1,5 @@
-"""Dev tool (GPU box): times the parts of the post chain (chain, bloom only, TAA only, one fused pair, literal passes), L2 flushed and warm.\nusage: python tools/post_parts.py [width height]"""
+"""Dev tool (GPU box): times the parts of the post chain (chain, bloom only, TAA only, one fused pair, literal passes), L2 flushed and warm.
+usage: python tools/post_parts.py [width height]"""
 import sys, numpy as np, torch
 sys.path.insert(0, __import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.abspath(__file__))))
 from opengl_raytracing_b200 import post as P, synthetic
