@@ -4,6 +4,7 @@
 //   rt_headless --scene default.scene --size 1920 1080 --frames 4 --out /tmp/frame
 //   rt_headless --dump-scene in.scene out.bin        (SceneIO only; needs no GPU)
 //   rt_headless --resave in.scene out.scene          (Load + Save round trip; needs no GPU)
+//   rt_headless --resave-v2 in.scene out.scene       (Load + SaveV2: the lossless OBJECT2 / LIGHT2 records)
 //
 // Outputs (row 0 = GL y 0): <out>_color.pfm, and with --raw also <out>_color.f32, <out>_position.f32
 // (RGBA32F) and <out>_normal.f16 (RGBA16F) — the three images the reference's post chain consumes.
@@ -21,7 +22,8 @@ static int usage() {
                "                   [--camera px py pz yaw pitch fov] [--noise FILE W H] [--skybox FILE SIZE CH f16|f32]\n"
                "                   [--device N] [--out PREFIX] [--raw]\n"
                "       rt_headless --dump-scene IN.scene OUT.bin\n"
-               "       rt_headless --resave IN.scene OUT.scene\n");
+               "       rt_headless --resave IN.scene OUT.scene\n"
+               "       rt_headless --resave-v2 IN.scene OUT.scene\n");
   return 2;
 }
 
@@ -43,17 +45,23 @@ static int dump_scene(const char* in, const char* out) {
   return 0;
 }
 
-static int resave(const char* in, const char* out) {
+static int resave(const char* in, const char* out, bool v2) {
   std::vector<Object> objects;
   std::vector<Light> lights;
   SceneNames names;
   if (!SceneIO::Load(in, objects, lights, &names)) { std::fprintf(stderr, "cannot open %s\n", in); return 1; }
-  return SceneIO::Save(out, objects, lights, &names) ? 0 : 1;
+  try {
+    return (v2 ? SceneIO::SaveV2(out, objects, lights, &names) : SceneIO::Save(out, objects, lights, &names)) ? 0 : 1;
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "rt_headless: %s\n", e.what());
+    return 1;
+  }
 }
 
 int main(int argc, char** argv) {
   if (argc >= 4 && std::string(argv[1]) == "--dump-scene") return dump_scene(argv[2], argv[3]);
-  if (argc >= 4 && std::string(argv[1]) == "--resave") return resave(argv[2], argv[3]);
+  if (argc >= 4 && std::string(argv[1]) == "--resave") return resave(argv[2], argv[3], false);
+  if (argc >= 4 && std::string(argv[1]) == "--resave-v2") return resave(argv[2], argv[3], true);
 
   std::string scene, out = "frame", noise_file, sky_file;
   int W = 800, H = 800, frames = 1, depth = 3, samples = 1, device = 0;   // src/global.cpp:4-5: 800 x 800

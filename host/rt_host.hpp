@@ -5,6 +5,7 @@
 //                                            src/Light.h:7-20) with the reference's default initialisers
 //   rtb200::GenerateAABBForObject          src/SceneIO.h:75-104
 //   rtb200::SceneIO::Load / Save           src/SceneIO.h:108-186 (the .scene text format)
+//   rtb200::SceneIO::SaveV2                the lossless OBJECT2 / LIGHT2 records (Load reads both kinds)
 //   rtb200::Camera                         src/Camera.h:7-42
 //   rtb200::SSBO / LightSSBO               src/SSBO.h, src/LightSSBO.h  (vector + update())
 //   rtb200::RaytracingShader               src/Shader.h:106-128 (use / set* by uniform name)
@@ -18,8 +19,10 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <initializer_list>
 #include <sstream>
 #include <stdexcept>
 #include <string>
@@ -160,8 +163,89 @@ class SceneIO {
         iss >> l.color[0] >> l.color[1] >> l.color[2] >> l.intensity >> l.radius >> l.samples;
         lights.push_back(l);
         if (names) names->lights.push_back(name);
+      } else if (kind == "OBJECT2") {          // the lossless record (WriteV2): every field the shader reads
+        Object o = MakeObject();
+        Material& m = o.material;
+        iss >> type >> name;
+        o.type = TypeV2(type, {"SPHERE", "PLANE"}, SPHERE);
+        iss >> o.position[0] >> o.position[1] >> o.position[2] >> o.radius >> o.normal[0] >> o.normal[1] >> o.normal[2] >> o.size[0] >> o.size[1];
+        iss >> m.type >> m.albedo[0] >> m.albedo[1] >> m.albedo[2] >> m.metallic >> m.roughness >> m.diffuseStrength >> m.ior >> m.transparency >>
+            m.specular >> m.subsurfaceScatter >> m.subsurfaceColor[0] >> m.subsurfaceColor[1] >> m.subsurfaceColor[2] >> m.scatterDistance;
+        GenerateAABBForObject(o);
+        objects.push_back(o);
+        if (names) names->objects.push_back(name);
+      } else if (kind == "LIGHT2") {
+        Light l = MakeLight();
+        iss >> type >> name;
+        l.type = TypeV2(type, {"POINT", "DIRECTIONAL", "AREA"}, POINT);
+        iss >> l.position[0] >> l.position[1] >> l.position[2] >> l.direction[0] >> l.direction[1] >> l.direction[2];
+        iss >> l.color[0] >> l.color[1] >> l.color[2] >> l.intensity >> l.radius >> l.samples;
+        iss >> l.shadowSoftness >> l.shadowType >> l.pcfSamples >> l.lightSize >> l.angularRadius;
+        lights.push_back(l);
+        if (names) names->lights.push_back(name);
       }
     }
+  }
+  // Type token of a v2 record: one of `known` (its position is the tag), or TYPE<n> for a tag the
+  // reference's enums do not name (never hit / black in the shader, but it must survive a round trip).
+  static int TypeV2(const std::string& word, std::initializer_list<const char*> known, int fallback) {
+    int tag = 0;
+    for (const char* k : known) { if (word == k) return tag; ++tag; }
+    if (word.compare(0, 4, "TYPE") == 0 && word.size() > 4) {
+      char* end = nullptr;
+      const long v = std::strtol(word.c_str() + 4, &end, 10);
+      if (end && *end == 0) return (int)v;
+    }
+    return fallback;
+  }
+  // The lossless text format: the reference's columns in their order plus
+  // diffuseStrength, the subsurface fields and the five shadow fields its own format drops
+  // (src/SceneIO.h:124-142). 9 significant digits round-trip every finite FP32 value. Bounds are
+  // recomputed on load. The reference's loader skips record kinds it does not know (:114-119).
+  static void WriteV2(std::ostream& out, const std::vector<Object>& objects, const std::vector<Light>& lights, const SceneNames* names = nullptr) {
+    auto num = [&](float v) {
+      if (!std::isfinite(v)) throw std::runtime_error("SceneIO::WriteV2: non-finite value in a scene record");
+      char buf[32];
+      std::snprintf(buf, sizeof(buf), " %.9g", (double)v);
+      out << buf;
+    };
+    auto tag = [&](int t, std::initializer_list<const char*> known) {
+      int i = 0;
+      for (const char* k : known) { if (i == t) { out << k; return; } ++i; }
+      out << "TYPE" << t;
+    };
+    out << "# rt-scene 2\n";
+    for (size_t i = 0; i < objects.size(); ++i) {
+      const Object& o = objects[i];
+      const Material& m = o.material;
+      out << "OBJECT2 ";
+      tag(o.type, {"SPHERE", "PLANE"});
+      out << ' ' << (names && i < names->objects.size() ? names->objects[i] : "Object" + std::to_string(i));
+      for (float v : {o.position[0], o.position[1], o.position[2], o.radius, o.normal[0], o.normal[1], o.normal[2], o.size[0], o.size[1]}) num(v);
+      out << ' ' << m.type;
+      for (float v : {m.albedo[0], m.albedo[1], m.albedo[2], m.metallic, m.roughness, m.diffuseStrength, m.ior, m.transparency, m.specular,
+                      m.subsurfaceScatter, m.subsurfaceColor[0], m.subsurfaceColor[1], m.subsurfaceColor[2], m.scatterDistance}) num(v);
+      out << '\n';
+    }
+    for (size_t i = 0; i < lights.size(); ++i) {
+      const Light& l = lights[i];
+      out << "LIGHT2 ";
+      tag(l.type, {"POINT", "DIRECTIONAL", "AREA"});
+      out << ' ' << (names && i < names->lights.size() ? names->lights[i] : "Light" + std::to_string(i));
+      for (float v : {l.position[0], l.position[1], l.position[2], l.direction[0], l.direction[1], l.direction[2], l.color[0], l.color[1], l.color[2], l.intensity, l.radius}) num(v);
+      out << ' ' << l.samples;
+      num(l.shadowSoftness);
+      out << ' ' << l.shadowType << ' ' << l.pcfSamples;
+      num(l.lightSize);
+      num(l.angularRadius);
+      out << '\n';
+    }
+  }
+  static bool SaveV2(const std::string& path, const std::vector<Object>& objects, const std::vector<Light>& lights, const SceneNames* names = nullptr) {
+    std::ofstream f(path);
+    if (!f.is_open()) return false;
+    WriteV2(f, objects, lights, names);
+    return (bool)f;
   }
   static bool Load(const std::string& path, std::vector<Object>& objects, std::vector<Light>& lights, SceneNames* names = nullptr) {
     std::ifstream f(path);

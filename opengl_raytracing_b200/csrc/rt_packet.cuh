@@ -787,8 +787,14 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 // arithmetic (-fmad=false: nothing contracts differently), bit-identical images; which one is
 // faster depends on the scene (B200: C3 39.5 -> 35.1 ms with 3, C5 10.9 -> 12.0 ms), so the host
 // times both on the first frames of a scene and keeps the faster (rt_abi.cu).
+// RT_PK_MINCTAS (dev A/B): resident CTAs per SM the small-scene kernel's registers are sized for.
+#ifdef RT_PK_MINCTAS
+#define PK_MIN_CTAS(big, minb) ((big) ? (minb) * 8 / RT_PK_WARPS : RT_PK_MINCTAS)
+#else
+#define PK_MIN_CTAS(big, minb) ((minb) * 8 / RT_PK_WARPS)
+#endif
 template <bool BIG, bool BANDS, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB * 8 / RT_PK_WARPS) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
+__global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const DeviceScene& sc = kp.sc;
   const rt_frame_params& fp = kp.fp;

@@ -206,6 +206,21 @@ class Scene:
 
 _OBJ_TYPES = {"SPHERE": SPHERE, "PLANE": PLANE}            # StringToObjectType, default SPHERE
 _LIGHT_TYPES = {"DIRECTIONAL": DIRECTIONAL, "AREA": AREA}   # StringToLightType, default POINT
+_LIGHT_TYPES_V2 = {"POINT": POINT, "DIRECTIONAL": DIRECTIONAL, "AREA": AREA}
+
+
+def _type_v2(word: str, names: dict, default: int) -> int:
+    """Type token of a v2 record: a known name, or ``TYPE<n>`` for a tag the reference's enums do
+    not name (the shader treats such an object as never hit and such a light as black, and both
+    must survive a save/load cycle)."""
+    if word in names:
+        return names[word]
+    if word.startswith("TYPE"):
+        try:
+            return int(word[4:])
+        except ValueError:
+            pass
+    return default
 
 
 def parse_scene(text: str) -> Scene:
@@ -239,6 +254,40 @@ def parse_scene(text: str) -> Scene:
             l["intensity"] = iss.float_(float(l["intensity"][0]))
             l["radius"] = iss.float_(float(l["radius"][0]))
             l["samples"] = iss.int_(int(l["samples"][0]))
+            lights.append(l)
+            lnames.append(name)
+        elif kind == "OBJECT2":                                # the lossless record (save_scene_v2)
+            o = new_objects(1)
+            type_str, name = iss.word(), iss.word()
+            o["type"] = _type_v2(type_str, _OBJ_TYPES, SPHERE)
+            o["position"][0] = [iss.float_(float(o["position"][0][k])) for k in range(3)]
+            o["radius"] = iss.float_(float(o["radius"][0]))
+            o["normal"][0] = [iss.float_(float(o["normal"][0][k])) for k in range(3)]
+            o["size"][0] = [iss.float_(float(o["size"][0][k])) for k in range(2)]
+            m = o["material"]
+            m["type"] = iss.int_(int(m["type"][0]))
+            m["albedo"][0] = [iss.float_(float(m["albedo"][0][k])) for k in range(3)]
+            for f in ("metallic", "roughness", "diffuseStrength", "ior", "transparency", "specular", "subsurfaceScatter"):
+                m[f] = iss.float_(float(m[f][0]))
+            m["subsurfaceColor"][0] = [iss.float_(float(m["subsurfaceColor"][0][k])) for k in range(3)]
+            m["scatterDistance"] = iss.float_(float(m["scatterDistance"][0]))
+            generate_aabb_for_object(o[0])
+            objs.append(o)
+            onames.append(name)
+        elif kind == "LIGHT2":
+            l = new_lights(1)
+            type_str, name = iss.word(), iss.word()
+            l["type"] = _type_v2(type_str, _LIGHT_TYPES_V2, POINT)
+            for f in ("position", "direction", "color"):
+                l[f][0] = [iss.float_(float(l[f][0][k])) for k in range(3)]
+            l["intensity"] = iss.float_(float(l["intensity"][0]))
+            l["radius"] = iss.float_(float(l["radius"][0]))
+            l["samples"] = iss.int_(int(l["samples"][0]))
+            l["shadowSoftness"] = iss.float_(float(l["shadowSoftness"][0]))
+            l["shadowType"] = iss.int_(int(l["shadowType"][0]))
+            l["pcfSamples"] = iss.int_(int(l["pcfSamples"][0]))
+            l["lightSize"] = iss.float_(float(l["lightSize"][0]))
+            l["angularRadius"] = iss.float_(float(l["angularRadius"][0]))
             lights.append(l)
             lnames.append(name)
     sc = Scene()
@@ -276,6 +325,46 @@ def save_scene(scene: Scene) -> str:
         vals = [*l["position"], *l["direction"], *l["color"], l["intensity"], l["radius"]]
         out.append(" ".join(["LIGHT", lnames.get(int(l["type"]), "POINT"), name] + [g(v) for v in vals]
                             + [str(int(l["samples"]))]))
+    return "\n".join(out) + "\n"
+
+
+def save_scene_v2(scene: Scene) -> str:
+    """The lossless text format: one ``OBJECT2`` / ``LIGHT2`` line per record holding
+    EVERY field the shader reads — the reference's ``OBJECT`` / ``LIGHT`` columns in their order,
+    plus ``diffuseStrength``, the subsurface fields and the five shadow fields the reference's
+    format drops (src/SceneIO.h:124-142). Floats are written with 9 significant
+    digits, which round-trips every finite FP32 value; ``inf`` / ``nan`` are not representable
+    in an istream extraction and are rejected. Bounds are not stored: ``GenerateAABBForObject``
+    recomputes them on load, as the reference does for every object it touches
+    (src/ImGUIManager.cpp:197). ``parse_scene`` and the C++ ``SceneIO::Parse`` read both record
+    kinds, in any mix; the reference's own loader skips lines whose first token it does not know
+    (src/SceneIO.h:114-119), so a v2 file is simply empty to it rather than mis-decoded."""
+    onames = {SPHERE: "SPHERE", PLANE: "PLANE"}
+    lnames = {POINT: "POINT", DIRECTIONAL: "DIRECTIONAL", AREA: "AREA"}
+
+    def g(v) -> str:
+        v = float(v)
+        if not math.isfinite(v):
+            raise ValueError("non-finite value in a scene record")
+        return "%.9g" % v
+
+    out = ["# rt-scene 2"]
+    for i, o in enumerate(scene.objects):
+        m = o["material"]
+        name = scene.object_names[i] if i < len(scene.object_names) else "Object%d" % i
+        vals = [*o["position"], o["radius"], *o["normal"], *o["size"]]
+        tail = [*m["albedo"], m["metallic"], m["roughness"], m["diffuseStrength"], m["ior"], m["transparency"],
+                m["specular"], m["subsurfaceScatter"], *m["subsurfaceColor"], m["scatterDistance"]]
+        t = int(o["type"])
+        out.append(" ".join(["OBJECT2", onames.get(t, "TYPE%d" % t), name] + [g(v) for v in vals]
+                            + [str(int(m["type"]))] + [g(v) for v in tail]))
+    for i, l in enumerate(scene.lights):
+        name = scene.light_names[i] if i < len(scene.light_names) else "Light%d" % i
+        t = int(l["type"])
+        vals = [*l["position"], *l["direction"], *l["color"], l["intensity"], l["radius"]]
+        out.append(" ".join(["LIGHT2", lnames.get(t, "TYPE%d" % t), name] + [g(v) for v in vals]
+                            + [str(int(l["samples"])), g(l["shadowSoftness"]), str(int(l["shadowType"])),
+                               str(int(l["pcfSamples"])), g(l["lightSize"]), g(l["angularRadius"])]))
     return "\n".join(out) + "\n"
 
 
