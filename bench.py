@@ -55,7 +55,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--stage", choices=["rt", "post"], default="rt",
+    ap.add_argument("--stage", choices=["rt", "post", "frame"], default="rt",
                     help="rt = the ray-tracing pass (the headline metric); post = the post chain (bench_post.py)")
     ap.add_argument("--config", type=int, default=2, help="BASELINE.json config number (1..5); the metric is quoted on 2")
     ap.add_argument("--scene", choices=["default", "SIMPLE", "performance_test"], default=None,
@@ -459,6 +459,10 @@ def main():
     if args.stage == "post":
         import bench_post
         (bench_post.run_reference if args.impl == "reference" else bench_post.run_ours)(args, emit)
+        return
+    if args.stage == "frame":
+        import bench_frame
+        (bench_frame.run_reference if args.impl == "reference" else bench_frame.run_ours)(args, emit)
         return
     if args.impl == "reference":
         run_reference(args)

@@ -6,6 +6,9 @@
 //   rt_headless --resave in.scene out.scene          (Load + Save round trip; needs no GPU)
 //   rt_headless --resave-v2 in.scene out.scene       (Load + SaveV2: the lossless OBJECT2 / LIGHT2 records)
 //
+//   rt_headless --scene default.scene --post --frames 8 --out /tmp/frame   (whole iterations: ray tracing +
+//                                        bloom + TAA on device-resident images; writes <out>_display.ppm)
+//
 // Outputs (row 0 = GL y 0): <out>_color.pfm, and with --raw also <out>_color.f32, <out>_position.f32
 // (RGBA32F) and <out>_normal.f16 (RGBA16F) — the three images the reference's post chain consumes.
 #include <chrono>
@@ -20,7 +23,7 @@ static int usage() {
   std::fprintf(stderr,
                "usage: rt_headless --scene FILE [--size W H] [--frames N] [--depth D] [--samples S] [--flags F]\n"
                "                   [--camera px py pz yaw pitch fov] [--noise FILE W H] [--skybox FILE SIZE CH f16|f32]\n"
-               "                   [--device N] [--out PREFIX] [--raw]\n"
+               "                   [--device N] [--out PREFIX] [--raw] [--post]\n"
                "       rt_headless --dump-scene IN.scene OUT.bin\n"
                "       rt_headless --resave IN.scene OUT.scene\n"
                "       rt_headless --resave-v2 IN.scene OUT.scene\n");
@@ -66,7 +69,7 @@ int main(int argc, char** argv) {
   std::string scene, out = "frame", noise_file, sky_file;
   int W = 800, H = 800, frames = 1, depth = 3, samples = 1, device = 0;   // src/global.cpp:4-5: 800 x 800
   int noise_w = 0, noise_h = 0, sky_size = 0, sky_ch = 4;
-  bool sky_f16 = true, raw = false, have_cam = false;
+  bool sky_f16 = true, raw = false, have_cam = false, post = false;
   unsigned flags = 0;
   float cam[6] = {0, 0, 0, -90, 0, 45};
   for (int i = 1; i < argc; ++i) {
@@ -81,6 +84,7 @@ int main(int argc, char** argv) {
     else if (a == "--device") { need(1); device = std::atoi(argv[++i]); }
     else if (a == "--out") { need(1); out = argv[++i]; }
     else if (a == "--raw") raw = true;
+    else if (a == "--post") post = true;
     else if (a == "--camera") { need(6); for (int k = 0; k < 6; ++k) cam[k] = (float)std::atof(argv[++i]); have_cam = true; }
     else if (a == "--noise") { need(3); noise_file = argv[++i]; noise_w = std::atoi(argv[++i]); noise_h = std::atoi(argv[++i]); }
     else if (a == "--skybox") { need(4); sky_file = argv[++i]; sky_size = std::atoi(argv[++i]); sky_ch = std::atoi(argv[++i]); sky_f16 = std::string(argv[++i]) == "f16"; }
@@ -110,13 +114,23 @@ int main(int argc, char** argv) {
     pipeline.numSamples = samples;
     pipeline.flags = flags;
     const auto t0 = std::chrono::steady_clock::now();
-    for (int f = 0; f < frames; ++f) pipeline.Render();
+    for (int f = 0; f < frames; ++f) {
+      if (post) pipeline.RenderFrame(raw && f == frames - 1);    // the whole iteration: ray tracing + bloom + TAA
+      else pipeline.Render();
+    }
     const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     std::printf("{\"scene\": \"%s\", \"objects\": %zu, \"lights\": %zu, \"width\": %d, \"height\": %d, \"frames\": %d, "
                 "\"ms_per_frame_host\": %.4f, \"launches\": %llu}\n",
                 scene.c_str(), pipeline.ssbo.objects.size(), pipeline.lightSSBO.lights.size(), W, H, frames, ms / frames,
                 (unsigned long long)rt_launch_count(pipeline.context()));
     const size_t px = (size_t)W * H;
+    if (post) {                                                  // what the window would show
+      if (!WritePPM(out + "_display.ppm", pipeline.displayTex.data(), W, H)) throw std::runtime_error("cannot write " + out + "_display.ppm");
+      if (raw && (!WriteRaw(out + "_display.rgba8", pipeline.displayTex.data(), px * 4) ||
+                  !WriteRaw(out + "_display.f32", pipeline.displayTexF.data(), px * 16)))
+        throw std::runtime_error("cannot write raw display outputs");
+      return 0;
+    }
     if (!WritePFM(out + "_color.pfm", pipeline.outputTex.data(), W, H)) throw std::runtime_error("cannot write " + out + "_color.pfm");
     if (raw) {
       const bool n32 = (flags & RT_FLAG_NORMAL_FP32) != 0;

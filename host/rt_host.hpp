@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "rt_abi.h"
+#include "rt_frame.h"
 
 namespace rtb200 {
 
@@ -390,7 +391,8 @@ class RaytracingShader {
 // The ray-tracing stage of ForwardShadingPipline (src/ForwardShadingPipeline.{h,cpp}): Init creates
 // the three output images (outputTex RGBA32F :57-65, gPositionTex RGBA32F :115-120, gNormalTex
 // RGBA16F :121-126); Render performs the :155-182 slice of one frame through rt_render_host.
-// Window, UI and the post chain are not part of this layer.
+// RenderFrame performs the whole iteration (ray tracing + post chain) through include/rt_frame.h.
+// Window and UI are not part of this layer.
 class ForwardShadingPipeline {
  public:
   ForwardShadingPipeline(int width = 800, int height = 800, int device = 0) : WIDTH(width), HEIGHT(height) {
@@ -400,7 +402,10 @@ class ForwardShadingPipeline {
   }
   ForwardShadingPipeline(const ForwardShadingPipeline&) = delete;
   ForwardShadingPipeline& operator=(const ForwardShadingPipeline&) = delete;
-  ~ForwardShadingPipeline() { if (ctx_) rt_destroy(ctx_); }
+  ~ForwardShadingPipeline() {
+    if (frame_) rt_frame_destroy(frame_);  // a frame goes before its context
+    if (ctx_) rt_destroy(ctx_);
+  }
 
   void Init() {
     const size_t px = (size_t)WIDTH * HEIGHT;
@@ -421,9 +426,7 @@ class ForwardShadingPipeline {
     return true;
   }
 
-  // One frame's ray-tracing stage. Outputs land in outputTex / gPositionTex / gNormalTex.
-  void Render() {
-    const bool upload = ssbo.dirty || lightSSBO.dirty;
+  void SetUniforms() {                     // :153-166
     RaytracingShader& sh = raytracingShader;
     sh.use();
     sh.setInt("numObjects", (int)ssbo.objects.size());
@@ -439,6 +442,12 @@ class ForwardShadingPipeline {
     rt_frame_params& p = sh.params;
     p.width = WIDTH; p.height = HEIGHT; p.row_begin = 0; p.row_end = HEIGHT;
     p.max_ray_depth = maxRayDepth; p.num_samples = numSamples; p.flags = flags;
+  }
+  // One frame's ray-tracing stage. Outputs land in outputTex / gPositionTex / gNormalTex.
+  void Render() {
+    const bool upload = ssbo.dirty || lightSSBO.dirty;
+    SetUniforms();
+    rt_frame_params& p = raytracingShader.params;
     if (upload)                            // ssbo.update() + lightSSBO.update() (src/SSBO.h:16-23)
       check(ctx_, rt_upload_scene(ctx_, ssbo.objects.data(), (int)ssbo.objects.size(), lightSSBO.lights.data(),
                                   (int)lightSSBO.lights.size(), nullptr, 0), "rt_upload_scene");
@@ -448,7 +457,50 @@ class ForwardShadingPipeline {
     if (taaEnabled) ++frameCount;          // the reference advances frameCount inside the TAA branch (:232-254)
   }
 
+  // The host's haltonSequence (src/global.cpp), float arithmetic, for the TAA jitter (:242-243).
+  static float haltonSequence(int index, int base) {
+    float f = 1.0f, r = 0.0f;
+    while (index > 0) {
+      f = f / (float)base;
+      r = r + f * (float)(index % base);
+      index = index / base;
+    }
+    return r;
+  }
+
+  // One WHOLE iteration of Render (:139-272) through rt_frame: ray tracing, bloom (threshold 1.0,
+  // 10 blurs, strength 0.5 — the values the reference hard-codes, :198/:208/:223), combine, TAA
+  // resolve into historyTex[frameCount % 2]; the three intermediate images stay on the device as
+  // the reference's GL textures do. The presented image lands in displayTex (8-bit UNORM, the
+  // window's framebuffer) — and, on request, in displayTexF (RGBA32F, before that conversion).
+  void RenderFrame(bool readFloat = false) {
+    if (!frame_) {
+      check(ctx_, rt_frame_create(ctx_, WIDTH, HEIGHT, &frame_), "rt_frame_create");
+      displayTex.reset((size_t)WIDTH * HEIGHT * 4);
+    }
+    SetUniforms();
+    rt_post_params pp;
+    std::memset(&pp, 0, sizeof(pp));
+    pp.width = WIDTH; pp.height = HEIGHT;
+    pp.bloom_threshold = 1.0f; pp.bloom_strength = 0.5f; pp.blur_passes = 10;
+    pp.taa_enabled = taaEnabled ? 1 : 0;
+    pp.taa_blend = taaBlendFactor;
+    pp.jitter_x = (float)(haltonSequence(frameCount % 8, 2) * 0.5 / WIDTH);      // double arithmetic, then setFloat
+    pp.jitter_y = (float)(haltonSequence(frameCount % 8, 3) * 0.5 / HEIGHT);
+    const bool upload = ssbo.dirty || lightSSBO.dirty;
+    check(ctx_, rt_frame_render_host(frame_, &raytracingShader.params, &pp, upload ? ssbo.objects.data() : nullptr, (int)ssbo.objects.size(),
+                                     upload ? lightSSBO.lights.data() : nullptr, (int)lightSSBO.lights.size(), displayTex.data(), RT_DISPLAY_RGBA8),
+          "rt_frame_render_host");
+    if (readFloat) {
+      if (displayTexF.size() == 0) displayTexF.reset((size_t)WIDTH * HEIGHT * 4);
+      check(ctx_, rt_frame_read_display(frame_, displayTexF.data(), RT_DISPLAY_RGBA32F, nullptr), "rt_frame_read_display");
+    }
+    ssbo.dirty = lightSSBO.dirty = false;
+    if (taaEnabled) ++frameCount;
+  }
+
   rt_context* context() { return ctx_; }
+  rt_frame* frame() { return frame_; }
 
   const int WIDTH, HEIGHT;                 // src/global.cpp:4-5
   Camera camera;
@@ -458,6 +510,9 @@ class ForwardShadingPipeline {
   RaytracingShader raytracingShader;
   HostImage<float> outputTex, gPositionTex;
   HostImage<uint16_t> gNormalTex;
+  HostImage<unsigned char> displayTex;     // RenderFrame: the window's 8-bit framebuffer
+  HostImage<float> displayTexF;            // RenderFrame(true): the same image before the 8-bit conversion
+  float taaBlendFactor = 0.1f;             // ImGUIManager's TAA blend slider default
   int frameCount = 0;
   int maxRayDepth = 3;
   int numSamples = 1;
@@ -467,6 +522,7 @@ class ForwardShadingPipeline {
 
  private:
   rt_context* ctx_ = nullptr;
+  rt_frame* frame_ = nullptr;
 };
 
 // ---------------------------------------------------------------- image writers (headless "display")
@@ -480,6 +536,19 @@ inline bool WritePFM(const std::string& path, const float* rgba, int w, int h) {
     for (int x = 0; x < w; ++x)
       for (int c = 0; c < 3; ++c) row[(size_t)x * 3 + c] = rgba[((size_t)y * w + x) * 4 + c];
     std::fwrite(row.data(), sizeof(float), row.size(), f);
+  }
+  return std::fclose(f) == 0;
+}
+// Binary PPM of an RGBA8 image, top row first (the GL image has row 0 at the bottom).
+inline bool WritePPM(const std::string& path, const unsigned char* rgba8, int w, int h) {
+  FILE* f = std::fopen(path.c_str(), "wb");
+  if (!f) return false;
+  std::fprintf(f, "P6\n%d %d\n255\n", w, h);
+  std::vector<unsigned char> row((size_t)w * 3);
+  for (int y = h - 1; y >= 0; --y) {
+    for (int x = 0; x < w; ++x)
+      for (int c = 0; c < 3; ++c) row[(size_t)x * 3 + c] = rgba8[((size_t)y * w + x) * 4 + c];
+    std::fwrite(row.data(), 1, row.size(), f);
   }
   return std::fclose(f) == 0;
 }

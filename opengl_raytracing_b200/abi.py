@@ -42,6 +42,13 @@ POST_EXPORTED_SYMBOLS = [                   # include/rt_post.h
 ]
 
 
+FRAME_EXPORTED_SYMBOLS = [                  # include/rt_frame.h
+    "rt_frame_create", "rt_frame_destroy", "rt_frame_render", "rt_frame_images", "rt_frame_read_display",
+    "rt_frame_render_host", "rt_frame_launch_count",
+]
+DISPLAY_RGBA32F, DISPLAY_RGBA8 = 0, 1
+
+
 class RtLibraryError(RuntimeError):
     pass
 
@@ -140,6 +147,17 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_post_chain.argtypes = [vp, pp, vp, vp, vp, vp, vp, vp]
     lib.rt_post_launch_count.argtypes = [vp]
     lib.rt_post_launch_count.restype = C.c_uint64
+    # include/rt_frame.h
+    fp = C.POINTER(FrameParams)
+    lib.rt_frame_create.argtypes = [vp, ip, ip, C.POINTER(vp)]
+    lib.rt_frame_destroy.argtypes = [vp]
+    lib.rt_frame_destroy.restype = None
+    lib.rt_frame_render.argtypes = [vp, fp, pp, vp]
+    lib.rt_frame_images.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.rt_frame_read_display.argtypes = [vp, vp, ip, vp]
+    lib.rt_frame_render_host.argtypes = [vp, fp, pp, vp, ip, vp, ip, vp, ip]
+    lib.rt_frame_launch_count.argtypes = [vp]
+    lib.rt_frame_launch_count.restype = C.c_uint64
     if path is None:
         _lib = lib
     return lib

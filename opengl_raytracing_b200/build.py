@@ -21,10 +21,11 @@ UNITS = [  # (source, extra flags)
     ("rt_kernel_parity.cu", ["-fmad=false"]),
     ("rt_abi.cu", []),
     ("rt_post.cu", ["-fmad=false"]),
+    ("rt_frame.cu", ["-fmad=false"]),
     ("rt_peak.cu", []),
 ]
 HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
-           os.path.join("..", "..", "include", "rt_post.h")]
+           os.path.join("..", "..", "include", "rt_post.h"), os.path.join("..", "..", "include", "rt_frame.h")]
 
 
 def _stale(target: str, deps: list) -> bool:

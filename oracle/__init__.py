@@ -180,6 +180,18 @@ def load_post(kind: str = "port") -> C.CDLL:
     return lib
 
 
+def display_rgba8(display: np.ndarray) -> np.ndarray:
+    """The window's default framebuffer (8-bit UNORM; no sRGB enable anywhere in the reference's
+    src/) as it stores the combine pass's colour (src/ForwardShadingPipeline.cpp:220-230):
+    OpenGL 4.3 section 2.3.4.2 / 17.3.9 — clamp to [0, 1], scale by 255 in FP32, round to nearest (GL leaves
+    the tie rule to the implementation: ties to even here), NaN -> 0. Checker of
+    rt_frame_read_display(RT_DISPLAY_RGBA8)."""
+    x = np.ascontiguousarray(display, dtype=np.float32)
+    x = np.where(np.isnan(x), np.float32(0), x)
+    x = np.clip(x, np.float32(0), np.float32(1)).astype(np.float32)
+    return np.rint(x * np.float32(255)).astype(np.uint8)
+
+
 def _img(a: np.ndarray, ch: int = 4) -> np.ndarray:
     a = np.ascontiguousarray(a, dtype=np.float32)
     assert a.ndim == 3 and a.shape[2] == ch, a.shape

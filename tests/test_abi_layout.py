@@ -1,4 +1,4 @@
-"""C-ABI library: loads and exports every symbol include/rt_abi.h and include/rt_post.h declare; the ctypes
+"""C-ABI library: loads and exports every symbol include/rt_abi.h, include/rt_post.h and include/rt_frame.h declare; the ctypes
 structures match the header's byte layouts. No compute calls (runs without a GPU)."""
 import ctypes as C
 import os
@@ -13,6 +13,7 @@ from opengl_raytracing_b200 import abi, scene as S
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "rt_abi.h")
 POST_HEADER = os.path.join(ROOT, "include", "rt_post.h")
+FRAME_HEADER = os.path.join(ROOT, "include", "rt_frame.h")
 
 
 def _declared_functions(header=HEADER):
@@ -25,13 +26,14 @@ def _declared_functions(header=HEADER):
 def test_header_functions_match_binding_list():
     assert _declared_functions() == sorted(abi.EXPORTED_SYMBOLS)
     assert _declared_functions(POST_HEADER) == sorted(abi.POST_EXPORTED_SYMBOLS)
+    assert _declared_functions(FRAME_HEADER) == sorted(abi.FRAME_EXPORTED_SYMBOLS)
 
 
 def test_library_loads_and_exports_every_symbol():
     from opengl_raytracing_b200 import build
     build.build()
     lib = abi.load_library()
-    for name in _declared_functions() + _declared_functions(POST_HEADER):
+    for name in _declared_functions() + _declared_functions(POST_HEADER) + _declared_functions(FRAME_HEADER):
         assert hasattr(lib, name), name
     assert lib.rt_abi_version() == 2
     assert lib.rt_status_string(5) == b"RT_ERR_UNAVAILABLE"

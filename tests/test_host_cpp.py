@@ -159,3 +159,45 @@ def test_cpp_v2_format_is_lossless_and_matches_python(headless, tmp_path, cfg):
     assert r.returncode == 0, r.stderr
     a, b = S.parse_scene(v1.read_text()), S.parse_scene(q.read_text())
     assert a.objects.tobytes() == b.objects.tobytes() and a.lights.tobytes() == b.lights.tobytes()
+
+
+@pytest.mark.gpu
+def test_headless_whole_frames_with_post_chain_match_python_frame(headless, tmp_path):
+    """rt_headless --post (ForwardShadingPipeline::RenderFrame: ray tracing + bloom + TAA on
+    device-resident images, lossless v2 scene file) against the Python Frame driven the same way:
+    the presented 8-bit image and the float display image of the third frame, bit for bit."""
+    from opengl_raytracing_b200 import abi, post as P
+    from opengl_raytracing_b200.frame import Frame
+    from opengl_raytracing_b200.pipeline import RtContext, bind_workload, workload_params
+    W, H = 256, 144
+    w = synthetic.config(2, W, H)
+    p = tmp_path / "c2_v2.scene"
+    p.write_text(S.save_scene_v2(S.Scene(objects=w.objects, lights=w.lights)))      # keeps the PCSS light
+    noise = tmp_path / "noise.r8"
+    w.noise.astype(np.uint8).tofile(noise)
+    sky = tmp_path / "sky.f16"
+    skyf = np.ascontiguousarray(w.skybox.astype(np.float16))
+    skyf.tofile(sky)
+    out = str(tmp_path / "g")
+    r = subprocess.run([headless, "--scene", str(p), "--size", str(W), str(H), "--frames", "3", "--raw", "--post", "--out", out,
+                        "--noise", str(noise), str(w.noise.shape[1]), str(w.noise.shape[0]),
+                        "--skybox", str(sky), str(skyf.shape[1]), str(skyf.shape[3]), "f16"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    d8 = np.fromfile(out + "_display.rgba8", dtype=np.uint8).reshape(H, W, 4)
+    d32 = np.fromfile(out + "_display.f32", dtype=np.float32).reshape(H, W, 4)
+    ctx = RtContext(0)
+    bind_workload(ctx, w)
+    fr = Frame(ctx, W, H)
+    for fc in range(3):
+        fr.render(workload_params(w, frame_count=fc), P.post_params(W, H, blend=0.1, jitter=P.taa_jitter(fc, W, H)))
+    want32 = fr.read_display(fmt=abi.DISPLAY_RGBA32F)
+    want8 = fr.read_display(fmt=abi.DISPLAY_RGBA8)
+    fr.close()
+    ctx.close()
+    assert d32.tobytes() == want32.tobytes()
+    assert d8.tobytes() == want8.tobytes()
+    ppm = open(out + "_display.ppm", "rb").read()
+    head = b"P6\n%d %d\n255\n" % (W, H)
+    assert ppm.startswith(head) and len(ppm) == len(head) + W * H * 3
+    assert ppm[len(head):len(head) + 3] == d8[H - 1, 0, :3].tobytes()            # top row first
