@@ -72,6 +72,22 @@ __device__ __forceinline__ float fract_(float a) { return a - floorf(a); }
 __device__ __forceinline__ f3 mix3(f3 a, f3 b, float t) { return a * (1.0f - t) + b * t; }
 __device__ __forceinline__ f3 reflect3(f3 I, f3 N) { return I - (2.0f * dot3(N, I)) * N; }
 
+// Multiply-add of colour-only and boolean-only code (BRDF terms, light evaluation, texture
+// filtering, shadow-ray set-up: nothing that feeds P, N or a bounce direction). Parity build: the
+// shader's two unfused operations, same operands (a*b + c; IEEE addition commutes, so the call
+// sites keep their bits). Fast build: one FFMA. The -fmad=false of the translation unit still
+// protects everything written with plain * and +.
+#if RT_PARITY
+__device__ __forceinline__ float smad(float a, float b, float c) { return a * b + c; }
+#else
+__device__ __forceinline__ float smad(float a, float b, float c) { return fmaf(a, b, c); }
+#endif
+__device__ __forceinline__ float sdot3(f3 a, f3 b) { return smad(a.z, b.z, smad(a.y, b.y, a.x * b.x)); }   // == dot3 in the parity build
+__device__ __forceinline__ f3 smad3(f3 a, float s, f3 c) { return mk3(smad(a.x, s, c.x), smad(a.y, s, c.y), smad(a.z, s, c.z)); }
+__device__ __forceinline__ f3 smad3(f3 a, f3 b, f3 c) { return mk3(smad(a.x, b.x, c.x), smad(a.y, b.y, c.y), smad(a.z, b.z, c.z)); }
+__device__ __forceinline__ f3 smix3(f3 a, f3 b, float t) { return smad3(b, t, a * (1.0f - t)); }                // == mix3
+__device__ __forceinline__ f3 normalize_color(f3 a) { return a * inversesqrt_shade(sdot3(a, a)); }              // == normalize_shade
+
 
 struct Mat {
   f3 albedo; float metallic, roughness, diffuseStrength, ior, transparency;
@@ -130,8 +146,8 @@ __device__ __forceinline__ f3 fetch_sky(const Textures& tx, f3 r) {
   else if (ay >= az)        { ma = ay; if (r.y >= 0.0f) { face = 2; sc = r.x; tc = r.z; } else { face = 3; sc = r.x; tc = -r.z; } }
   else                      { ma = az; if (r.z >= 0.0f) { face = 4; sc = r.x; tc = -r.y; } else { face = 5; sc = -r.x; tc = -r.y; } }
   const int S = tx.sky_size;
-  float u = 0.5f * (div_ieee(sc, ma) + 1.0f) * (float)S - 0.5f;
-  float v = 0.5f * (div_ieee(tc, ma) + 1.0f) * (float)S - 0.5f;
+  float u = smad(0.5f * (div_ieee(sc, ma) + 1.0f), (float)S, -0.5f);
+  float v = smad(0.5f * (div_ieee(tc, ma) + 1.0f), (float)S, -0.5f);
   if (!(u == u)) u = 0.0f;
   if (!(v == v)) v = 0.0f;
   const float hi = (float)(S - 1);
@@ -144,9 +160,7 @@ __device__ __forceinline__ f3 fetch_sky(const Textures& tx, f3 r) {
   const uint2* f = tx.sky + (size_t)face * S * S;
   const f3 t00 = unpack_rgb16f(__ldg(f + j0 * S + i0)), t10 = unpack_rgb16f(__ldg(f + j0 * S + i1));
   const f3 t01 = unpack_rgb16f(__ldg(f + j1 * S + i0)), t11 = unpack_rgb16f(__ldg(f + j1 * S + i1));
-  const f3 top = t00 * (1.0f - a) + t10 * a;
-  const f3 bot = t01 * (1.0f - a) + t11 * a;
-  return top * (1.0f - w) + bot * w;
+  return smix3(smix3(t00, t10, a), smix3(t01, t11, a), w);
 }
 
 // ---------------------------------------------------------------- samplers (glsl:273-313)
@@ -198,22 +212,22 @@ __device__ __forceinline__ float halton3(int i) { return i < kHaltonTable ? c_ha
 // fresnelSchlick (glsl:220-223)
 __device__ __forceinline__ float fresnel_schlick(float cosTheta, float ior) {
   const float r0 = pow2(div_shade(1.0f - ior, 1.0f + ior));
-  return r0 + (1.0f - r0) * pow5(1.0f - cosTheta);
+  return smad(1.0f - r0, pow5(1.0f - cosTheta), r0);
 }
 
 // computePBR (glsl:226-253): GGX NDF, Schlick-GGX geometry, Schlick Fresnel, kD/F split.
 __device__ __forceinline__ f3 compute_pbr(const Mat& mat, f3 N, f3 V, f3 L, f3 H, f3 radiance) {
   const float alpha = pow2(mat.roughness);
   const float a2 = alpha * alpha;
-  const float NdotH = fmaxf(dot3(N, H), 0.0f);
-  const float NDF = div_shade(a2, kPi * pow2(pow2(NdotH) * (a2 - 1.0f) + 1.0f));
+  const float NdotH = fmaxf(sdot3(N, H), 0.0f);
+  const float NDF = div_shade(a2, kPi * pow2(smad(pow2(NdotH), a2 - 1.0f, 1.0f)));
   const float k = pow2(mat.roughness + 1.0f) / 8.0f;
-  const float NdotV = fmaxf(dot3(N, V), 0.0f), NdotL = fmaxf(dot3(N, L), 0.0f);
-  float G = div_shade(NdotV, NdotV * (1.0f - k) + k);
-  G *= div_shade(NdotL, NdotL * (1.0f - k) + k);
-  const f3 F0 = mix3(mk3(0.04f, 0.04f, 0.04f), mat.albedo, mat.metallic);
-  const float p5 = pow5(1.0f - fmaxf(dot3(H, V), 0.0f));
-  const f3 F = F0 + mk3(1.0f - F0.x, 1.0f - F0.y, 1.0f - F0.z) * p5;
+  const float NdotV = fmaxf(sdot3(N, V), 0.0f), NdotL = fmaxf(sdot3(N, L), 0.0f);
+  float G = div_shade(NdotV, smad(NdotV, 1.0f - k, k));
+  G *= div_shade(NdotL, smad(NdotL, 1.0f - k, k));
+  const f3 F0 = smix3(mk3(0.04f, 0.04f, 0.04f), mat.albedo, mat.metallic);
+  const float p5 = pow5(1.0f - fmaxf(sdot3(H, V), 0.0f));
+  const f3 F = smad3(mk3(1.0f - F0.x, 1.0f - F0.y, 1.0f - F0.z), p5, F0);
   const f3 numerator = (NDF * G) * F;
   const float denominator = 4.0f * NdotV * NdotL;
   const float dd = fmaxf(denominator, 0.001f);

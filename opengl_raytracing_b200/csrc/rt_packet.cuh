@@ -70,10 +70,10 @@ __device__ __forceinline__ f3 normalize_shadow(f3 a) { return normalize_ieee(a);
 // zero / denormal / infinite components down the generic path), so nothing is flushed.
 #if RT_PK_NO_FTZ
 __device__ __forceinline__ float rcp_shadow(float x) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-__device__ __forceinline__ f3 normalize_shadow(f3 a) { return a * rsqrtf(dot3(a, a)); }
+__device__ __forceinline__ f3 normalize_shadow(f3 a) { return a * rsqrtf(sdot3(a, a)); }
 #else
 __device__ __forceinline__ float rcp_shadow(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-__device__ __forceinline__ f3 normalize_shadow(f3 a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(dot3(a, a))); return a * r; }
+__device__ __forceinline__ f3 normalize_shadow(f3 a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(sdot3(a, a))); return a * r; }
 #endif
 #endif
 
@@ -130,15 +130,19 @@ __device__ __forceinline__ bool sphere_t(float4 sp, f3 o, f3 d, float a, float& 
 
 // "near root in (0, lim)" for shadow rays. Parity build: the literal root. Fast build: the
 // same predicate without sqrt/div — t>0 <=> b<0 && c>0 (a>0); t<lim <=> sqrt(disc) > -b-2a*lim.
-__device__ __forceinline__ bool sphere_any(f3 oc, float cc, f3 d, float a, float lim) {
+// The fast form takes two per-ray constants hoisted out of the candidate loop: m4a = -4a and
+// m2al = -2a*lim (unused in the parity build).
+__device__ __forceinline__ bool sphere_any(f3 oc, float cc, f3 d, float a, float lim, float m4a, float m2al) {
+#if RT_PARITY
   const float b = 2.0f * dot3(oc, d);
   const float disc = b * b - 4.0f * a * cc;
-#if RT_PARITY
   if (disc < 0.0f) return false;
   const float t = div_ieee(-b - sqrt_ieee(disc), 2.0f * a);
   return t > 0.0f && t < lim;
 #else
-  const float q = -b - 2.0f * a * lim;
+  const float b = 2.0f * sdot3(oc, d);
+  const float disc = fmaf(b, b, m4a * cc);
+  const float q = m2al - b;
   return disc >= 0.0f && b < 0.0f && cc > 0.0f && (q < 0.0f || disc > q * q);
 #endif
 }
@@ -427,12 +431,13 @@ __device__ __noinline__ bool trace_any_one(const Scene& s, const Cands& cd, cons
 // zero / denormal / infinite component goes through the generic single-ray routine.
 __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands& cd, const Cone& cone, f3 o,
                                                      const f3 (&d)[4], unsigned active, float lim) {
-  float a[4];
+  float a[4], m4a[4], m2al[4];
   float2 ivx[4], ivy[4], ivz[4];
   unsigned signs = 0u, remaining = active, occ = 0u;       // signs: 3 bits per ray
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
-    a[r] = dot3(d[r], d[r]);
+    a[r] = sdot3(d[r], d[r]);
+    m4a[r] = -4.0f * a[r]; m2al[r] = -2.0f * a[r] * lim;
     signs |= ((__float_as_uint(d[r].x) >> 31) | ((__float_as_uint(d[r].y) >> 31) << 1) | ((__float_as_uint(d[r].z) >> 31) << 2)) << (3 * r);
     ivx[r] = dup2(rcp_shadow(d[r].x)); ivy[r] = dup2(rcp_shadow(d[r].y)); ivz[r] = dup2(rcp_shadow(d[r].z));   // FMUL2 takes the scalar broadcast form
     if (((active >> r) & 1u) && !dir_regular(d[r], a[r])) {
@@ -474,10 +479,10 @@ __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands
       if (is_sphere) {
         const float4 sp = lds128(rec + 48u);
         const f3 oc = o - xyz(sp);
-        const float cc = dot3(oc, oc) - sp.w * sp.w;
+        const float cc = smad(-sp.w, sp.w, sdot3(oc, oc));                 // dot(oc,oc) - r*r
 #pragma unroll
         for (int r = 0; r < 4; ++r)
-          if (pass[r] && !((occ >> r) & 1u) && sphere_any(oc, cc, d[r], a[r], lim)) occ |= 1u << r;
+          if (pass[r] && !((occ >> r) & 1u) && sphere_any(oc, cc, d[r], a[r], lim, m4a[r], m2al[r])) occ |= 1u << r;
       } else {
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
@@ -547,8 +552,12 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
   const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin);
   if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
-  const f3 tangent = normalize_ieee(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
+  // (the frame only steers shadow rays: single-MUFU normalisation in the fast build; 0 * inf is NaN in both)
+  const f3 tangent = normalize_shadow(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
   const f3 bitangent = cross3(lightDir, tangent);
+#if !RT_PARITY
+  const f3 tangent_fs = tangent * filterSize, bitangent_fs = bitangent * filterSize;
+#endif
   int unoccluded = 0;
   int j = 0;
   while (j < total) {
@@ -568,7 +577,11 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
           const int i = idx - nprobe;
           const float rx = fract_(halton2(i) + noise_r);                                     // glsl:366-367
           const float ry = fract_(halton3(i) + 0.0f);
+#if RT_PARITY
           f3 v = (lightDir + (rx * tangent) * filterSize) + (ry * bitangent) * filterSize;   // glsl:371-378
+#else
+          f3 v = smad3(bitangent_fs, ry, smad3(tangent_fs, rx, lightDir));                   // same point, fused
+#endif
           if (light.type != 1) v = normalize_shadow(v);
           d[r] = v;
         }
@@ -632,13 +645,34 @@ __device__ __forceinline__ bool phase_any(bool pred) {
 #endif
 }
 
+// length(v) and normalize(v) of a light vector (glsl:463-466, :477-479). Parity build: the shader's
+// sqrt(dot) and v * (1 / sqrt(dot)), IEEE. Fast build: r = rsqrt(dot), length = dot * r, unit = v * r.
+__device__ __forceinline__ void unit_and_length(f3& v, float& len) {
+#if RT_PARITY
+  len = sqrt_ieee(dot3(v, v));
+  v = normalize_ieee(v);
+#else
+  const float dd = sdot3(v, v);
+  const float r = inversesqrt_shade(dd);
+  len = dd * r;
+  v = v * r;
+#endif
+}
+__device__ __forceinline__ f3 normalize_light(f3 v) {
+#if RT_PARITY
+  return normalize_ieee(v);
+#else
+  return normalize_color(v);
+#endif
+}
+
 // computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
 // lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
 // Every lane of the CTA walks the light loop (lit = this lane has a surface to shade).
 template <bool BIG>
 __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, int coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
   f3 Lo = mk3(0.0f, 0.0f, 0.0f);
-  const f3 shadow_origin = P + N * 0.001f;               // glsl:381, :412
+  const f3 shadow_origin = smad3(N, 0.001f, P);          // glsl:381, :412 (P + N * 0.001)
 #pragma unroll 1
   for (int i = 0; i < s.nl; ++i) {
     phase_sync(coh >= 3);
@@ -646,24 +680,28 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     const LightRec light = load_light(s, i);
     f3 lightDir = mk3(0.0f, 0.0f, 0.0f);
     float attenuation = 1.0f, lightDistance = 0.0f;
+    // lightDir / lightDistance feed the BRDF (colour) and the shadow rays (a boolean each), never P, N
+    // or a bounce direction: the fast build takes length and unit vector from one MUFU.RSQ.
     if (light.type == 0) {
       lightDir = light.position - P;
-      lightDistance = sqrt_ieee(dot3(lightDir, lightDir));
-      attenuation = div_shade(1.0f, 1.0f + 0.1f * lightDistance + 0.01f * lightDistance * lightDistance);
-      lightDir = normalize_ieee(lightDir);
+      unit_and_length(lightDir, lightDistance);
+      attenuation = div_shade(1.0f, smad(0.01f * lightDistance, lightDistance, smad(0.1f, lightDistance, 1.0f)));
     } else if (light.type == 1) {
-      lightDir = normalize_ieee(-light.direction);
+      lightDir = normalize_light(-light.direction);
       lightDistance = 1e6f;
     } else if (light.type == 2) {
       lightDir = light.position - P;
-      lightDistance = sqrt_ieee(dot3(lightDir, lightDir));
-      lightDir = normalize_ieee(lightDir);
+      unit_and_length(lightDir, lightDistance);
       attenuation = div_shade(1.0f, lightDistance * lightDistance);
-      const f3 lightNormal = normalize_shade(light.direction);
-      attenuation *= fmaxf(dot3(lightDir, lightNormal), 0.0f);   // P->light vs facing
+      const f3 lightNormal = normalize_color(light.direction);
+      attenuation *= fmaxf(sdot3(lightDir, lightNormal), 0.0f);   // P->light vs facing
     }
-    const f3 L = normalize_shade(lightDir);
-    const f3 H = normalize_shade(V + L);
+#if RT_PARITY
+    const f3 L = normalize_shade(lightDir);              // glsl:493: normalises the unit vector once more
+#else
+    const f3 L = lightDir;                               // (a second normalisation moves it by <= 1 ulp)
+#endif
+    const f3 H = normalize_color(V + L);
     const f3 radiance = (light.color * attenuation) * light.intensity;
     const f3 brdf = compute_pbr(mat, N, V, L, H, radiance);
     const bool sampled = light.shadowType == 1 || light.shadowType == 2;
@@ -672,7 +710,7 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
     if (light.shadowType == 0) shadowFactor = 1.0f;
     else if (sampled) shadowFactor = shadow_packets<BIG>(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
-    Lo = Lo + brdf * shadowFactor;
+    Lo = smad3(brdf, shadowFactor, Lo);
   }
   if (lit && mat.subsurfaceScatter > 0.0f) {
     const Scene s2 = s; const Mat mat2 = mat;                                           // copies: see trace_closest
@@ -724,7 +762,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
       const Hit h = trace_closest<BIG>(s, cand_base, ro, rd);
       if (h.code < 0) {                         // miss path (glsl:530-534)
         const f3 sky = fp.use_skybox ? fetch_sky(tx, rd) : mk3(0.0f, 0.0f, 0.0f);
-        out.color = out.color + throughput * sky;
+        out.color = smad3(throughput, sky, out.color);
         alive = false;
       } else {
         lit = true;
@@ -733,13 +771,13 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
         else N = xyz(lds128(s.pln + (unsigned)(h.code - s.ns) * kPlaneBytes + 48u));
         mat = load_material(s, index);
         P = ro + rd * h.t;
-        V = normalize_shade(-rd);
+        V = normalize_color(-rd);
         out.P = P; out.N = N; out.object_id = index;
       }
     }
     const f3 Lo = compute_lighting<BIG>(s, cand_base, coh, lit, noise_r, P, N, mat, V);
     if (!lit) continue;
-    out.color = out.color + throughput * Lo;
+    out.color = smad3(throughput, Lo, out.color);
 
     if (depth > 2) {                            // Russian roulette (glsl:544-549)
       const float diffuseWeight = sqrt_ieee(dot3(mat.albedo, mat.albedo)) * mat.diffuseStrength;
