@@ -31,7 +31,7 @@ struct rt_context {
   int n_obj = 0, n_planes = 0, n_lights = 0;
   size_t off_plane = 0, off_material = 0, off_lights = 0;   // in float4 units
   // packet-kernel blob (appended to the same device buffer)
-  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0, pk_clusters = 0;
+  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0, pk_clusters = 0, pk_fan_ok = 0;
   // textures
   uint2* d_sky = nullptr; cudaArray_t sky_array = nullptr; cudaTextureObject_t sky_tex = 0; int sky_size = 0;
   unsigned char* d_noise = nullptr; int noise_w = 0, noise_h = 0;
@@ -46,6 +46,7 @@ struct rt_context {
   // Auto: frame 1 of a new (scene shape, frame shape) runs untimed, frames 2 and 3 time one build
   // each with events on the caller's stream, frame 4 reads the two times and keeps the faster.
   int dense_override = -1;      // RT_PK_DENSE=0/1 pins the choice
+  int fan_override = -1;        // dev A/B: RT_PK_FAN=0 disables the analytic PCSS probe classification of the fast build
   struct Tune { long long key[8] = {-1, 0, 0, 0, 0, 0, 0, 0}; int state = 0; int choice = 0; cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}; } tune;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t band_done[16] = {};
@@ -132,7 +133,7 @@ void stage_scene(const rt_object* obj, int n, const rt_light* lights, int m, int
 // Object[]/Light[] -> the packet kernel's shared-memory image (layout in rt_packet.cuh).
 // Returns the size in float4 units, or 0 when the scene cannot use the sign-select loops
 // (a non-finite bound). `out` may be null to size only.
-struct PkLayout { size_t float4s; int spheres, planes, lights_offset, clusters; };
+struct PkLayout { size_t float4s; int spheres, planes, lights_offset, clusters, fan_ok; };
 
 inline unsigned morton10(unsigned v) {                   // spread 10 bits to every third position
   v &= 1023u;
@@ -144,12 +145,25 @@ inline unsigned morton10(unsigned v) {                   // spread 10 bits to ev
 }
 
 PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights, int m, float4* out) {
-  PkLayout L = {0, 0, 0, 0, 0};
+  PkLayout L = {0, 0, 0, 0, 0, 1};
   for (int i = 0; i < n; ++i) {
     if (obj[i].type == 0) L.spheres++; else if (obj[i].type == 1) L.planes++;
     if (obj[i].type == 0 || obj[i].type == 1)
       for (int k = 0; k < 3; ++k)
-        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0, 0};
+        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0, 0, 0};
+    // fan_ok: every sphere's box contains the sphere (what GenerateAABBForObject produces). The
+    // fast build's analytic PCSS probe classification (rt_packet.cuh probe_fan) relies on "a ray
+    // that hits the sphere with margin also passes its box"; any other box sends probes down the
+    // exact per-ray path.
+    if (obj[i].type == 0) {
+      const float r = std::fabs(obj[i].radius);
+      if (!(r > 0.0f) || !std::isfinite(r)) L.fan_ok = 0;
+      for (int k = 0; k < 3; ++k) {
+        const float lo = std::fmin(obj[i].bounds.min[k], obj[i].bounds.max[k]), hi = std::fmax(obj[i].bounds.min[k], obj[i].bounds.max[k]);
+        const float c = obj[i].position[k];
+        if (!(lo <= c - r && hi >= c + r)) L.fan_ok = 0;
+      }
+    }
   }
   // Sphere clusters (rt_packet.cuh "two-level boxes"): from kPkClusterMinSpheres spheres on, the
   // sphere slots are ordered along a Morton curve of their centres and every kPkClusterSize
@@ -317,6 +331,7 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if ((e = rt::upload_tables_parity(h2, h3t, order)) != cudaSuccess) return bail(e);
   if (const char* e2 = getenv("RT_PK_COHERENT")) c->coherent_override = atoi(e2);
   if (const char* e3 = getenv("RT_PK_DENSE")) c->dense_override = atoi(e3);
+  if (const char* e4 = getenv("RT_PK_FAN")) c->fan_override = atoi(e4);
   *out = c;
   return RT_OK;
 }
@@ -374,6 +389,9 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
   c->off_plane = off_plane; c->off_material = off_material; c->off_lights = off_lights;
   c->off_pk = off_pk; c->pk_float4s = pkl.float4s; c->pk_spheres = pkl.spheres; c->pk_planes = pkl.planes;
   c->pk_lights_offset = pkl.lights_offset; c->pk_clusters = pkl.clusters;
+  bool has_pcss = false;                                 // the analytic probe path only pays where a PCSS light exists
+  for (int j = 0; j < m; ++j) has_pcss = has_pcss || ((const rt_light*)lights)[j].shadowType == 2;
+  c->pk_fan_ok = (pkl.fan_ok && has_pcss) ? 1 : 0;
   if (async) {
     RT_CUDA(c, cudaEventRecord(c->stage_done, stream));
     c->stage_pending = true;
@@ -493,6 +511,7 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   sc.pk_num_clusters = c->pk_clusters;
+  sc.pk_fan_ok = c->fan_override >= 0 ? (c->fan_override && c->pk_fan_ok) : c->pk_fan_ok;
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);
   // with long loops the barrier imbalance costs more than the fetch locality gains.
   sc.pk_big = c->pk_spheres + c->pk_planes > 48 ? 1 : 0;

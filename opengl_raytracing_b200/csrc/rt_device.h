@@ -52,6 +52,7 @@ struct DeviceScene {
   int pk_lights_offset;      // bytes from the start of the blob
   int pk_big;                // 1: large-scene kernel (independent warps, two-level boxes)
   int pk_coherent;           // 1: CTA-coherent phases (small scenes), 0: independent warps
+  int pk_fan_ok;             // 1: every sphere's box contains its sphere (analytic PCSS probe classification allowed)
   int pk_dense;              // large-scene kernel only: 1 = the 80-register build (3 CTAs / 24 warps per SM), 0 = 128 registers (2 / 16)
 };
 

@@ -315,7 +315,7 @@ __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3
 // comparison carries a 4e-6*|v|^2 slack (40x the rounding of d2 - along^2, and above the
 // 1e-7*|v|^2 by which the shader's own discriminant can report a grazing hit).
 struct Cone { f3 L; float s, c2, far; f3 fn; float fe; };   // axis, sin bound, cos^2 bound, far = lim*(1+e); fan plane normal (0 = none), PCF slack
-struct Cands { saddr base; int n; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test)
+struct Cands { saddr base; int n, first, nsph; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test); list entries [first, n), the first nsph of [0, n) are spheres
 
 __device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 center, float r) {
   const f3 v = center - o;
@@ -340,6 +340,11 @@ __device__ __forceinline__ bool cone_misses_plane(const Cone& c, f3 o, saddr rec
   const float slack = pb.y * (c.s + 1.0e-5f);               // |n.delta| <= |n| e (+ rounding)
   // every denominator n.d has one strict sign and the numerator the opposite (or zero): t <= 0
   if ((s0 <= 0.0f && nl > slack) || (s0 >= 0.0f && nl < -slack)) return true;
+  // t = s0 / (n.d) with |n.d| <= |n| |d| and |d| <= 1 + e: a plane farther than that from the origin
+  // is beyond every ray's limit (far already carries the (1 + e) factor; NaN: not culled)
+#if !RT_PK_NO_PLANE_FAR
+  if (fabsf(s0) > c.far * pb.y * (1.0f + c.s)) return true;
+#endif
   return cone_misses_sphere(c, o, xyz(pp), pb.x);
 }
 
@@ -351,7 +356,7 @@ __device__ __forceinline__ int cand_code(const Cands& cd, int i) { return cd.lis
 // One scan of the scene per shadow job. Returns the candidate set for the job's packets.
 template <bool BIG>
 __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base, bool cone_ok, const Cone& cone, f3 o) {
-  Cands cd; cd.base = cand_base; cd.n = s.ns + s.np; cd.list = false; cd.prefilter = false;
+  Cands cd; cd.base = cand_base; cd.n = s.ns + s.np; cd.first = 0; cd.nsph = s.ns; cd.list = false; cd.prefilter = false;
   if (!cone_ok) return cd;
   int n = 0;
   if (BIG && s.nc > 0) {                                     // cluster bounding spheres first, then members
@@ -382,6 +387,7 @@ __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base
       ++n;
     }
   }
+  cd.nsph = n;
   saddr rec = s.pln;
   for (int j = 0; j < s.np; ++j, rec += kPlaneBytes) {
     if (cone_misses_plane(cone, o, rec)) continue;
@@ -403,7 +409,7 @@ __device__ __noinline__ bool trace_any_one(const Scene& s, const Cands& cd, cons
   const f3 inv = regular ? mk3(rcp_shadow(d.x), rcp_shadow(d.y), rcp_shadow(d.z)) : mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
   const unsigned ox = (regular && d.x < 0.0f) ? 8u : 0u, oy = (regular && d.y < 0.0f) ? 24u : 16u, oz = (regular && d.z < 0.0f) ? 40u : 32u;
 #pragma unroll 1
-  for (int i = 0; i < cd.n; ++i) {
+  for (int i = cd.first; i < cd.n; ++i) {
     const int code = cand_code(cd, i);
     const saddr rec = record_of(s, code);
     if (cd.prefilter && (code < s.ns ? cone_misses_sphere(cone, o, xyz(lds128(rec + 48u)), lds32(rec + 60u)) : cone_misses_plane(cone, o, rec))) continue;
@@ -460,7 +466,7 @@ __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands
     remaining &= ~group;
     const unsigned ox = (lead & 1u) ? 8u : 0u, oy = (lead & 2u) ? 24u : 16u, oz = (lead & 4u) ? 40u : 32u;
 #pragma unroll 1
-    for (int i = 0; i < cd.n; ++i) {
+    for (int i = cd.first; i < cd.n; ++i) {
       const int code = cand_code(cd, i);
       PK_STAT(6, 1);
       const saddr rec = record_of(s, code);
@@ -520,10 +526,57 @@ __device__ __forceinline__ Mat load_material(const Scene& s, int index) {
   return m;
 }
 
+#if !RT_PARITY
+// Fast build only: the 16 PCSS probes of one job decided analytically. Probe k leaves the job's
+// origin along u(x) = L + x*(1,1,1), x = 2*rv_k*searchSize (glsl:408-409; the normalisation does
+// not change what it hits). For a sphere (centre c, radius r), with oc = o - c and cc = oc.oc - r^2:
+//     B(x) = oc.u = A0 + A1 x,   U(x) = u.u = LL + 2 Lw x + 3 x^2,
+//     the ray hits the sphere (near root > 0)  <=>  cc > 0,  B(x) < 0,  p(x) = B^2 - U cc >= 0,
+// and p is a quadratic in x whose three coefficients are per (job, sphere) constants. Every probe
+// is classified as a sure hit (p > tol and B < -tol), a sure miss (p < -tol or B > tol) or
+// undecided, with tol = 1e-4 x the magnitude of the terms that cancel (100 x their rounding). A
+// sure hit on any candidate means "a blocker exists" (glsl:425); sure misses on all of them mean
+// "fully lit" (glsl:428-430); one undecided probe, a sphere that reaches beyond the light
+// (t < lightDistance would matter) or a sphere too small for its distance sends the job down the
+// exact per-ray packets; plane candidates always take the exact packets (over the planes alone
+// when every sphere is a sure miss). Out of line, scalar arguments: small scenes without a PCSS
+// light keep their instruction footprint. The host guarantees box >= sphere (fan_ok), so a
+// sure hit also passes the slab test.  Returns 0 none blocked, 1 blocked, 2 undecided.
+__device__ __noinline__ int probe_fan(saddr sph, saddr cand_base, int nsph, f3 o, f3 L, float searchSize, float lim) {
+  const float LL = sdot3(L, L), Lw = (L.x + L.y) + L.z, xs = 2.0f * searchSize;
+  bool undecided = false;
+#pragma unroll 1
+  for (int i = 0; i < nsph; ++i) {
+    const float4 sp = lds128(sph + (unsigned)cand_load(cand_base, i) * kSphereBytes + 48u);
+    const f3 oc = o - xyz(sp);
+    const float d2 = sdot3(oc, oc);
+    const float cc = smad(-sp.w, sp.w, d2);                             // the packets' own expression: same bits
+    if (!(cc > 0.0f)) continue;                                         // origin inside / on the sphere: the near root is <= 0
+    const float r = fabsf(sp.w), dist = sqrt_shade(d2);
+    if (!(dist + r < lim * 0.9999f) || !(r * 1000.0f > dist)) { undecided = true; continue; }
+    const float A0 = sdot3(oc, L), A1 = (oc.x + oc.y) + oc.z;
+    const float q2 = smad(A1, A1, -3.0f * cc), q1 = smad(A0, A1, -Lw * cc), q0 = smad(A0, A0, -LL * cc);
+    const float acc = fabsf(cc);
+    const float m2 = smad(A1, A1, 3.0f * acc) * 1.0e-4f, m1 = (fabsf(A0 * A1) + fabsf(Lw) * acc) * 2.0e-4f, m0 = smad(A0, A0, LL * acc) * 1.0e-4f;
+    const float aA0 = fabsf(A0) * 1.0e-4f, aA1 = fabsf(A1) * 1.0e-4f;
+#pragma unroll 4
+    for (int k = 0; k < 16; ++k) {
+      const float x = c_probe_rv[k] * xs, ax = fabsf(x);
+      const float p = smad(smad(q2, x, 2.0f * q1), x, q0);
+      const float tol = smad(smad(m2, ax, m1), ax, m0);
+      const float B = smad(A1, x, A0), tolB = smad(aA1, ax, aA0);
+      if (p > tol && B < -tolB) return 1;
+      if (!(p < -tol || B > tolB)) undecided = true;
+    }
+  }
+  return undecided ? 2 : 0;
+}
+#endif
+
 // calculateShadow (glsl:442-455) for shadowType 1 (pcfShadow, glsl:342-397) and 2 (pcssShadow,
 // glsl:400-440 = "fully lit unless one of 16 fixed probes is blocked, else PCF"). Probes and PCF
 // samples run through ONE packet site: jobs [0,nprobe) are probes, [nprobe,nprobe+pcf) samples.
-template <bool BIG>
+template <bool BIG, bool FAN>
 __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
                                                 f3 lightDir, float lightDistance) {
   const int nprobe = light.shadowType == 2 ? 16 : 0;
@@ -560,6 +613,17 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
 #endif
   int unoccluded = 0;
   int j = 0;
+  int probe_first = 0;                                   // exact probe packets visit candidates [probe_first, n)
+#if !RT_PARITY
+  if (FAN && nprobe && cd.list && cd.nsph > 0) {
+    const int verdict = probe_fan(s.sph, cd.base, cd.nsph, origin, lightDir, searchSize, lim_probe);
+    if (verdict == 1) j = nprobe;                        // a blocker exists: straight to the PCF phase
+    else if (verdict == 0) {
+      if (cd.nsph == cd.n) return 1.0f;                  // glsl:428-430: no blocker -> fully lit
+      probe_first = cd.nsph;                             // no sphere blocks: the planes decide, exactly
+    }
+  }
+#endif
   while (j < total) {
     const bool probing = j < nprobe;
     const int end = probing ? nprobe : total;
@@ -589,7 +653,9 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
         d[r] = d[0];
       }
     }
-    const unsigned occ = trace_any_packet(s, cd, cone, origin, d, active, probing ? lim_probe : lim_pcf) & active;
+    Cands cdj = cd;
+    if (FAN) cdj.first = probing ? probe_first : 0;
+    const unsigned occ = trace_any_packet(s, cdj, cone, origin, d, active, probing ? lim_probe : lim_pcf) & active;
     if (probing) {
       if (occ) { j = nprobe; continue; }                 // a blocker exists: go to the PCF phase
       j += 4;
@@ -669,7 +735,7 @@ __device__ __forceinline__ f3 normalize_light(f3 v) {
 // computeLighting (glsl:457-507). The BRDF term is evaluated before the shadow factor so that
 // lights which cannot contribute skip their shadow rays (Lo + 0*finite == Lo exactly).
 // Every lane of the CTA walks the light loop (lit = this lane has a surface to shade).
-template <bool BIG>
+template <bool BIG, bool FAN>
 __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, int coh, bool lit, float noise_r, f3 P, f3 N, const Mat& mat, f3 V) {
   f3 Lo = mk3(0.0f, 0.0f, 0.0f);
   const f3 shadow_origin = smad3(N, 0.001f, P);          // glsl:381, :412 (P + N * 0.001)
@@ -709,7 +775,7 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     if (brdf.x == 0.0f && brdf.y == 0.0f && brdf.z == 0.0f && (!sampled || light.pcfSamples > 0)) continue;
     float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
     if (light.shadowType == 0) shadowFactor = 1.0f;
-    else if (sampled) shadowFactor = shadow_packets<BIG>(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
+    else if (sampled) shadowFactor = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
     Lo = smad3(brdf, shadowFactor, Lo);
   }
   if (lit && mat.subsurfaceScatter > 0.0f) {
@@ -725,7 +791,7 @@ struct PixelResult { f3 color, P, N; int object_id; };
 // One invocation of the shader's main() per lane. Whole warps (coh: the whole CTA) call this
 // together; `alive` = this lane still has a path to extend (false from the start for lanes
 // outside the image). The bounce loop ends when no lane of the warp / CTA is alive.
-template <bool BIG>
+template <bool BIG, bool FAN>
 __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const Scene& s, const Textures& tx, saddr cand_base, int coh,
                                                    bool alive, unsigned px, unsigned py, int frame_count) {
   const rt_frame_params& fp = kp.fp;
@@ -775,7 +841,7 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
         out.P = P; out.N = N; out.object_id = index;
       }
     }
-    const f3 Lo = compute_lighting<BIG>(s, cand_base, coh, lit, noise_r, P, N, mat, V);
+    const f3 Lo = compute_lighting<BIG, FAN>(s, cand_base, coh, lit, noise_r, P, N, mat, V);
     if (!lit) continue;
     out.color = smad3(throughput, Lo, out.color);
 
@@ -831,7 +897,11 @@ __device__ __forceinline__ PixelResult shade_pixel(const KernelParams& kp, const
 #else
 #define PK_MIN_CTAS(big, minb) ((minb) * 8 / RT_PK_WARPS)
 #endif
-template <bool BIG, bool BANDS, int MINB>
+// FAN = true: the fast build's analytic PCSS probe classification (probe_fan) is compiled in; chosen
+// by the host when the scene has a PCSS light and every sphere's box contains its sphere. A
+// separate instantiation because the mere presence of that code costs the small-scene kernel 3.5 %
+// on scenes that never run it (C1 0.1075 -> 0.111 ms, same box).
+template <bool BIG, bool BANDS, int MINB, bool FAN>
 __global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const DeviceScene& sc = kp.sc;
@@ -904,7 +974,7 @@ __global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_ke
     PixelResult r;                                       // position/normal/id: those of sample 0
 #pragma unroll 1
     for (int sidx = 0; sidx < nsamp; ++sidx) {           // colour: sequential FP32 sum over samples
-      const PixelResult r2 = shade_pixel<BIG>(kp, s, tx, cand_base, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
+      const PixelResult r2 = shade_pixel<BIG, FAN>(kp, s, tx, cand_base, coh, inside, (unsigned)px, (unsigned)py, fp.frame_count + sidx);
       if (sidx == 0) r = r2;
       else r.color = r.color + r2.color;
     }
@@ -937,13 +1007,13 @@ inline cudaError_t upload_probe_order(const float* halton3, const int* order16) 
   return cudaMemcpyToSymbol(c_probe_rv, rv, sizeof(rv));
 }
 
-template <bool BIG, bool BANDS, int MINB>
+template <bool BIG, bool BANDS, int MINB, bool FAN>
 inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
-  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel<BIG, BANDS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel<BIG, BANDS, MINB, FAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel<BIG, BANDS, MINB>, kThreads, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel<BIG, BANDS, MINB, FAN>, kThreads, smem);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
@@ -956,21 +1026,27 @@ inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStr
   // tile + one failing fetch per warp; coherent mode = one per block + one per CTA.
   if (!BIG && kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
   else *warps_launched = ctas * kWarpsPerCta;
-  rt_packet_kernel<BIG, BANDS, MINB><<<ctas, kThreads, smem, stream>>>(kp);
+  rt_packet_kernel<BIG, BANDS, MINB, FAN><<<ctas, kThreads, smem, stream>>>(kp);
   return cudaGetLastError();
 }
 
-// kp.sc.pk_big (host-chosen by object count) selects the kernel.
-inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+// kp.sc.pk_big (host-chosen by object count) selects the kernel; kp.sc.pk_fan_ok the FAN instantiation
+// (fast build only: the parity build has no analytic path and instantiates FAN = false alone).
+template <bool BANDS, bool FAN>
+inline cudaError_t launch_packet_f(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   constexpr int kMinB = RT_PK_MINBLOCKS;
-  if (kp.fp.row_band > 0) {
-    if (!kp.sc.pk_big) return launch_packet_t<false, true, kMinB>(kp, sm_count, stream, warps_launched);
-    return kp.sc.pk_dense ? launch_packet_t<true, true, 3>(kp, sm_count, stream, warps_launched)
-                          : launch_packet_t<true, true, kMinB>(kp, sm_count, stream, warps_launched);
-  }
-  if (!kp.sc.pk_big) return launch_packet_t<false, false, kMinB>(kp, sm_count, stream, warps_launched);
-  return kp.sc.pk_dense ? launch_packet_t<true, false, 3>(kp, sm_count, stream, warps_launched)
-                        : launch_packet_t<true, false, kMinB>(kp, sm_count, stream, warps_launched);
+  if (!kp.sc.pk_big) return launch_packet_t<false, BANDS, kMinB, FAN>(kp, sm_count, stream, warps_launched);
+  return kp.sc.pk_dense ? launch_packet_t<true, BANDS, 3, FAN>(kp, sm_count, stream, warps_launched)
+                        : launch_packet_t<true, BANDS, kMinB, FAN>(kp, sm_count, stream, warps_launched);
+}
+inline cudaError_t launch_packet(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
+#if !RT_PARITY
+  if (kp.sc.pk_fan_ok)
+    return kp.fp.row_band > 0 ? launch_packet_f<true, true>(kp, sm_count, stream, warps_launched)
+                              : launch_packet_f<false, true>(kp, sm_count, stream, warps_launched);
+#endif
+  return kp.fp.row_band > 0 ? launch_packet_f<true, false>(kp, sm_count, stream, warps_launched)
+                            : launch_packet_f<false, false>(kp, sm_count, stream, warps_launched);
 }
 
 }  // namespace pk

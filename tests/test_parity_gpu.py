@@ -110,6 +110,34 @@ def test_packet_kernel_is_bit_identical_on_edge_cases(rt_ctx, name):
     assert _bits_equal(a, b) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}, name
 
 
+@pytest.mark.parametrize("n,size", [(2, (960, 540)), (3, (480, 270)), (4, (240, 136))])
+def test_analytic_probe_classification_matches_exact_probes(monkeypatch, n, size):
+    """Fast build: the 16 PCSS probes of a job are decided analytically (probe_fan: sure hit / sure
+    miss with a 1e-4 tolerance band, anything else falls back to the exact per-ray packets), so the
+    image must be the one the exact probes give (RT_PK_FAN=0): a probe can only be classified
+    differently inside the band, and there the fallback runs. Also with boxes that do NOT contain
+    their spheres (the host then disables the analytic path: identical by construction)."""
+    from opengl_raytracing_b200.pipeline import RtContext
+    w = synthetic.config(n, *size)
+    if n == 4:
+        w.num_samples = 4
+    shrunk = synthetic.config(n, *size)
+    shrunk.num_samples = w.num_samples
+    shrunk.objects["bounds"]["max"][::3] -= np.float32(0.05)      # every third box cut short
+    for wl in (w, shrunk):
+        outs = {}
+        for fan in ("0", "1"):
+            monkeypatch.setenv("RT_PK_FAN", fan)
+            c = RtContext(0)
+            outs[fan] = render_workload(c, wl, flags=abi.FLAG_NORMAL_FP32)
+            c.close()
+        assert _bits_equal(outs["0"], outs["1"])["position"] == 0 and _bits_equal(outs["0"], outs["1"])["object_id"] == 0
+        with np.errstate(invalid="ignore"):
+            bad = (np.abs(outs["0"]["color"] - outs["1"]["color"]) > 1e-3).any(axis=-1)
+        assert bad.mean() <= 1e-4, (n, int(bad.sum()))
+    monkeypatch.delenv("RT_PK_FAN")
+
+
 def test_fast_packet_kernel_stays_close_to_fast_literal_kernel(rt_ctx):
     """Fast build: the packet kernel additionally approximates shadow-ray setup (MUFU rcp/rsqrt,
     root-free sphere occlusion). Those can only flip a shadow sample at an exact silhouette."""
