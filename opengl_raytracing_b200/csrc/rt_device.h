@@ -10,7 +10,10 @@ namespace rt {
 
 // Packet-kernel sphere clusters: every kPkClusterSize consecutive sphere slots share one
 // cluster record; built from kPkClusterMinSpheres spheres on (rt_abi.cu stage_scene_packet).
-constexpr int kPkClusterSize = 16;
+#ifndef RT_PK_CLUSTER
+#define RT_PK_CLUSTER 16
+#endif
+constexpr int kPkClusterSize = RT_PK_CLUSTER;   // (dev A/B: -DRT_PK_CLUSTER=8)
 constexpr int kPkClusterMinSpheres = 64;
 
 // Device-resident scene in the layout the kernel stages into shared memory. Built on the

@@ -146,8 +146,14 @@ __device__ __forceinline__ f3 fetch_sky(const Textures& tx, f3 r) {
   else if (ay >= az)        { ma = ay; if (r.y >= 0.0f) { face = 2; sc = r.x; tc = r.z; } else { face = 3; sc = r.x; tc = -r.z; } }
   else                      { ma = az; if (r.z >= 0.0f) { face = 4; sc = r.x; tc = -r.y; } else { face = 5; sc = -r.x; tc = -r.y; } }
   const int S = tx.sky_size;
+  const float rma = div_shade(1.0f, ma);               // colour-only: one MUFU.RCP in the fast build, 1/ma * sc ...
+#if RT_PARITY
   float u = smad(0.5f * (div_ieee(sc, ma) + 1.0f), (float)S, -0.5f);
   float v = smad(0.5f * (div_ieee(tc, ma) + 1.0f), (float)S, -0.5f);
+#else
+  float u = smad(smad(sc, rma, 1.0f) * 0.5f, (float)S, -0.5f);
+  float v = smad(smad(tc, rma, 1.0f) * 0.5f, (float)S, -0.5f);
+#endif
   if (!(u == u)) u = 0.0f;
   if (!(v == v)) v = 0.0f;
   const float hi = (float)(S - 1);
