@@ -41,13 +41,16 @@ struct rt_context {
   uint64_t launches = 0;
   // e2e path
   int host_path = RT_HOST_PATH_AUTO;
-  int coherent_override = -1;   // dev A/B: RT_PK_COHERENT=0/1
-  // Large-scene kernel: 128-register (2 CTAs/SM) vs 80-register (3 CTAs/SM) build, identical images.
-  // Auto: frame 1 of a new (scene shape, frame shape) runs untimed, frames 2 and 3 time one build
-  // each with events on the caller's stream, frame 4 reads the two times and keeps the faster.
-  int dense_override = -1;      // RT_PK_DENSE=0/1 pins the choice
+  int coherent_override = -1;   // RT_PK_COHERENT=0..3 pins the phase level (both kernels)
+  // Large-scene kernel: 128-register (2 CTAs/SM) vs 80-register (3 CTAs/SM) build, each with independent
+  // warps or CTA-coherent phases (level 3) — four variants, identical images. Which is fastest depends
+  // on the scene (B200: C3 32.9 ms independent/128, 19.3 ms coherent/80; C5 10.7 ms independent/128,
+  // 12.5 ms coherent/80). Auto: frame 1 of a new (scene shape, frame shape) runs untimed, the next
+  // frames time one variant each with events on the caller's stream, the frame after reads the
+  // times and keeps the fastest.
+  int dense_override = -1;      // RT_PK_DENSE=0/1 pins the register budget
   int fan_override = -1;        // dev A/B: RT_PK_FAN=0 disables the analytic PCSS probe classification of the fast build
-  struct Tune { long long key[8] = {-1, 0, 0, 0, 0, 0, 0, 0}; int state = 0; int choice = 0; cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}; } tune;
+  struct Tune { long long key[8] = {-1, 0, 0, 0, 0, 0, 0, 0}; int state = 0; int choice = 0; cudaEvent_t ev[4][2] = {}; } tune;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t band_done[16] = {};
   cudaStream_t stream = nullptr;
@@ -341,7 +344,7 @@ void rt_destroy(rt_context* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   rt::post_release(c->post_state);
-  for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) if (c->tune.ev[i][j]) cudaEventDestroy(c->tune.ev[i][j]);
+  for (int i = 0; i < 4; ++i) for (int j = 0; j < 2; ++j) if (c->tune.ev[i][j]) cudaEventDestroy(c->tune.ev[i][j]);
   if (c->sky_tex) cudaDestroyTextureObject(c->sky_tex);
   if (c->sky_array) cudaFreeArray(c->sky_array);
   cudaFree(c->d_sky); cudaFree(c->d_noise); cudaFree(c->d_scene);
@@ -520,36 +523,46 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   // few phases for the barriers to pay (C1 0.1033 / 0.1053 / 0.1074 ms).
   sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : (p->max_ray_depth <= 1 ? 1 : 3);
   const bool par = (p->flags & RT_FLAG_PARITY_MATH) != 0u;
-  // ---- register-budget choice for the large-scene kernel (see rt_context::Tune)
+  // ---- variant choice for the large-scene kernel (see rt_context::Tune)
   sc.pk_dense = 0;
-  int timed = -1;                                          // 0 / 1: this launch is a timed trial of that build
+  int timed = -1;                                          // >= 0: this launch is a timed trial of that variant
   if (use_packet && sc.pk_big) {
     rt_context::Tune& t = c->tune;
-    if (c->dense_override >= 0) {
-      sc.pk_dense = c->dense_override ? 1 : 0;
-    } else {
+    int vd[4], vc[4], nv = 0;                              // candidate (register budget, phase level) pairs
+    for (int coh = 0; coh <= 3; coh += 3)
+      for (int dense = 0; dense <= 1; ++dense) {
+        if (c->dense_override >= 0 && dense != (c->dense_override ? 1 : 0)) continue;
+        if (c->coherent_override >= 0 && coh != 0) continue;
+        vd[nv] = dense; vc[nv] = c->coherent_override >= 0 ? c->coherent_override : coh; ++nv;
+      }
+    int pick = 0;
+    if (nv > 1) {
       const long long key[8] = {c->pk_spheres, c->pk_planes, c->n_lights, p->width, (long long)kp.tiles_y, p->max_ray_depth,
-                                p->num_samples, (long long)(par ? 1 : 0) | ((long long)(p->row_band > 0) << 1)};
+                                p->num_samples, (long long)(par ? 1 : 0) | ((long long)(p->row_band > 0) << 1) | ((long long)nv << 2)};
       if (std::memcmp(key, t.key, sizeof(key)) != 0) { std::memcpy(t.key, key, sizeof(key)); t.state = 0; t.choice = 0; }
       if (t.state == 0) {                                  // first frame: untimed (cold caches, module load)
-        if (!t.ev[0][0]) for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) RT_CUDA(c, cudaEventCreate(&t.ev[i][j]));
+        if (!t.ev[0][0]) for (int i = 0; i < 4; ++i) for (int j = 0; j < 2; ++j) RT_CUDA(c, cudaEventCreate(&t.ev[i][j]));
         t.state = 1;
-      } else if (t.state == 1 || t.state == 2) {
-        timed = t.state - 1; sc.pk_dense = timed; t.state += 1;
-      } else if (t.state == 3) {                           // both trials are at least one frame old
-        float ms[2] = {0.0f, 0.0f};
-        bool ok = true;
-        for (int i = 0; i < 2; ++i) {
-          ok = ok && cudaEventSynchronize(t.ev[i][1]) == cudaSuccess && cudaEventElapsedTime(&ms[i], t.ev[i][0], t.ev[i][1]) == cudaSuccess;
+      } else if (t.state <= nv) {
+        timed = t.state - 1; pick = timed; t.state += 1;
+      } else if (t.state == nv + 1) {                      // every trial is at least one frame old
+        float best = 0.0f;
+        int arg = 0;
+        for (int i = 0; i < nv; ++i) {
+          float ms = 0.0f;
+          const bool ok = cudaEventSynchronize(t.ev[i][1]) == cudaSuccess && cudaEventElapsedTime(&ms, t.ev[i][0], t.ev[i][1]) == cudaSuccess;
+          if (!ok) { cudaGetLastError(); arg = 0; break; }
+          if (i == 0 || ms < best) { best = ms; arg = i; }
         }
-        if (!ok) cudaGetLastError();
-        t.choice = (ok && ms[1] < ms[0]) ? 1 : 0;
-        t.state = 4;
-        sc.pk_dense = t.choice;
+        t.choice = arg;
+        t.state = nv + 2;
+        pick = t.choice;
       } else {
-        sc.pk_dense = t.choice;
+        pick = t.choice;
       }
     }
+    sc.pk_dense = vd[pick];
+    sc.pk_coherent = vc[pick];
   }
   unsigned warps = 0;
   cudaError_t e;

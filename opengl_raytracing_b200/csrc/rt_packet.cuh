@@ -945,7 +945,7 @@ __global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_ke
   //    no_instruction), tile-level coherence alone gave +52 % throughput.
   //  * independent (large scenes): every warp pulls its own tiles from the global counter; the
   //    object loops are long, cheap sky tiles and expensive reflective tiles balance dynamically.
-  const int coh = BIG ? 0 : sc.pk_coherent;   // 0 independent warps; 1 CTA blocks; 2 + barrier per bounce; 3 + barrier per light
+  const int coh = sc.pk_coherent;   // 0 independent warps; 1 CTA blocks; 2 + barrier per bounce; 3 + barrier per light
   __shared__ unsigned s_tile;
   unsigned tile = 0, next = 0;
   if (!coh) {
@@ -1024,7 +1024,7 @@ inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStr
   // how far the work counter advances during this launch (reported through *warps_launched
   // as "advance - num_tiles", the form rt_render adds back): independent mode = one fetch per
   // tile + one failing fetch per warp; coherent mode = one per block + one per CTA.
-  if (!BIG && kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
+  if (kp.sc.pk_coherent) *warps_launched = kp.blocks_x * kp.blocks_y + ctas - num_tiles;
   else *warps_launched = ctas * kWarpsPerCta;
   rt_packet_kernel<BIG, BANDS, MINB, FAN><<<ctas, kThreads, smem, stream>>>(kp);
   return cudaGetLastError();

@@ -77,8 +77,8 @@ def test_packet_kernel_is_bit_identical_to_literal_kernel(rt_ctx, n):
 @pytest.mark.parametrize("n", [3, 4, 5])
 def test_register_budget_builds_are_bit_identical_and_autotune_is_stable(monkeypatch, n):
     """The large-scene kernel exists as a 128-register (2 CTAs/SM) and an 80-register (3 CTAs/SM)
-    build of the same source; the library times both on the first frames of a scene and keeps the
-    faster. Whatever it picks, every frame must be the same image: both pinned builds (fast and
+    build of the same source, each run with independent warps or CTA-coherent phases; the library
+    times the four variants on the first frames of a scene and keeps the fastest. Whatever it picks, every frame must be the same image: both pinned builds (fast and
     IEEE math) and six consecutive auto-tuned frames are compared bit for bit."""
     from opengl_raytracing_b200.pipeline import RtContext
     w = synthetic.config(n, *FULLISH[n])
@@ -86,19 +86,23 @@ def test_register_budget_builds_are_bit_identical_and_autotune_is_stable(monkeyp
         w.num_samples = 2
     outs = {}
     for dense in ("0", "1"):
-        monkeypatch.setenv("RT_PK_DENSE", dense)
-        c = RtContext(0)
-        outs[dense] = (render_workload(c, w, flags=abi.FLAG_NORMAL_FP32),
-                       render_workload(c, w, flags=abi.FLAG_NORMAL_FP32 | abi.FLAG_PARITY_MATH, bind=False))
-        c.close()
+        for coh in ("0", "3"):                   # independent warps / CTA-coherent phases: the other tuned dimension
+            monkeypatch.setenv("RT_PK_DENSE", dense)
+            monkeypatch.setenv("RT_PK_COHERENT", coh)
+            c = RtContext(0)
+            outs[dense + coh] = (render_workload(c, w, flags=abi.FLAG_NORMAL_FP32),
+                                 render_workload(c, w, flags=abi.FLAG_NORMAL_FP32 | abi.FLAG_PARITY_MATH, bind=False))
+            c.close()
     for k in (0, 1):
-        assert _bits_equal(outs["0"][k], outs["1"][k]) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
+        for v in ("03", "10", "13"):
+            assert _bits_equal(outs["00"][k], outs[v][k]) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
     monkeypatch.delenv("RT_PK_DENSE")
+    monkeypatch.delenv("RT_PK_COHERENT")
     c = RtContext(0)
-    frames = [render_workload(c, w, flags=abi.FLAG_NORMAL_FP32, bind=(i == 0)) for i in range(6)]
+    frames = [render_workload(c, w, flags=abi.FLAG_NORMAL_FP32, bind=(i == 0)) for i in range(8)]   # 1 untimed + 4 trials + choice
     c.close()
     for f in frames:
-        assert _bits_equal(f, outs["0"][0]) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
+        assert _bits_equal(f, outs["00"][0]) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
 
 
 @pytest.mark.parametrize("name", sorted(edge_workloads().keys()))
