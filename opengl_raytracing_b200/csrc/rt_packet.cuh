@@ -314,9 +314,13 @@ __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3
 // Conservative: sin is over-, cos under-estimated, radii are inflated by 1e-3, and the squared
 // comparison carries a 4e-6*|v|^2 slack (40x the rounding of d2 - along^2, and above the
 // 1e-7*|v|^2 by which the shader's own discriminant can report a grazing hit).
-struct Cone { f3 L; float s, c2, far; f3 fn; float fe; };   // axis, sin bound, cos^2 bound, far = lim*(1+e); fan plane normal (0 = none), PCF slack
+struct Cone { f3 L; float s, c2, far; f3 fn; float fe; bool fan; };   // axis, sin bound, cos^2 bound, far = lim*(1+e); fan plane normal (0 = none), PCF slack
 struct Cands { saddr base; int n, first, nsph; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test); list entries [first, n), the first nsph of [0, n) are spheres
 
+// FANSKIP: branch around the fan-plane test when the job has no probes. Worth about 1 % in the
+// small-scene kernel's sphere scan (same-box A/B on C2); in the large-scene kernel's long scan loops
+// the branch costs more than the 8 instructions it saves (C3 19.3 -> 20.3 ms): straight-line there.
+template <bool FANSKIP = false>
 __device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 center, float r) {
   const f3 v = center - o;
   const float along = fmaf(v.z, c.L.z, fmaf(v.y, c.L.y, v.x * c.L.x));
@@ -329,6 +333,7 @@ __device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 cente
   // PCSS fan: the 16 probes all lie in the plane through o spanned by L and (1,1,1) (glsl:409 adds
   // the same scalar to x, y and z), the PCF samples within fe of L: a sphere farther than that from
   // the plane is out of reach. fn = 0 (no probes, or L || (1,1,1)) disables the test.
+  if (FANSKIP && !c.fan) return false;                      // no probes in this job (or L || (1,1,1)): fn = 0, nothing to test
   const float w = fmaf(v.z, c.fn.z, fmaf(v.y, c.fn.y, v.x * c.fn.x));
   return fabsf(w) > fmaf(sqrtf(d2) * 1.001f + rr, c.fe, rr);
 }
@@ -382,7 +387,7 @@ __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base
 #pragma unroll 2
     for (int k = 0; k < s.ns; ++k, rec += kSphereBytes) {
       const float4 sp = lds128(rec + 48u);
-      if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
+      if (cone_misses_sphere<!BIG>(cone, o, xyz(sp), sp.w)) continue;
       if (n < kCandCap) cand_store(cand_base, n, k);
       ++n;
     }
@@ -595,11 +600,12 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   cone.c2 = (1.0f - cone.s * cone.s) * 0.999f;
   cone.far = fmaxf(lim_pcf, lim_probe) * (1.0f + cone.s) * 1.0001f;              // NaN limits: fmaxf keeps the other
   cone.fn = mk3(0.0f, 0.0f, 0.0f);
+  cone.fan = false;
   cone.fe = e_pcf * 1.01f + 2.0e-5f;              // + the rounding of a probe direction off its plane
   if (nprobe) {
     const f3 fx = cross3(lightDir, mk3(0.57735026f, 0.57735026f, 0.57735026f));
     const float f2 = dot3(fx, fx);
-    if (f2 > 1.0e-4f) cone.fn = fx * rsqrtf(f2);
+    if (f2 > 1.0e-4f) { cone.fn = fx * rsqrtf(f2); cone.fan = true; }
   }
   const float ll = dot3(lightDir, lightDir);
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
