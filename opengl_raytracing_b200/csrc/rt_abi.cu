@@ -50,6 +50,10 @@ struct rt_context {
   // times and keeps the fastest.
   int dense_override = -1;      // RT_PK_DENSE=0/1 pins the register budget
   int fan_override = -1;        // dev A/B: RT_PK_FAN=0 disables the analytic PCSS probe classification of the fast build
+  int grid_override = -1;       // dev A/B: RT_PK_GRID=0 disables the light grids of large scenes
+  // light grids (build_light_grids): cached while the uploaded bytes do not change (the reference re-uploads every frame)
+  std::vector<unsigned char> grid_key; std::vector<float4> grid_data; int grid_off_f4 = 0, grid_ent_f4 = 0;
+  size_t off_grid = 0, grid_f4s = 0;
   struct Tune { long long key[8] = {-1, 0, 0, 0, 0, 0, 0, 0}; int state = 0; int choice = 0; cudaEvent_t ev[4][2] = {}; } tune;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t band_done[16] = {};
@@ -147,6 +151,209 @@ inline unsigned morton10(unsigned v) {                   // spread 10 bits to ev
   return v;
 }
 
+// Slot order of the spheres in the packet blob: array order, or Morton order of the centres when clustered.
+std::vector<int> sphere_slot_order(const rt_object* obj, int n, bool clustered) {
+  std::vector<int> order;
+  for (int i = 0; i < n; ++i) if (obj[i].type == 0) order.push_back(i);
+  if (clustered) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i : order) for (int k = 0; k < 3; ++k) {
+      const float v = obj[i].position[k];
+      if (v < lo[k]) lo[k] = v;
+      if (v > hi[k]) hi[k] = v;
+    }
+    std::vector<std::pair<unsigned, int>> keyed;
+    keyed.reserve(order.size());
+    for (int i : order) {
+      unsigned code = 0;
+      for (int k = 0; k < 3; ++k) {
+        const float ext = hi[k] - lo[k];
+        float q = ext > 0.f ? (obj[i].position[k] - lo[k]) / ext * 1023.f : 0.f;
+        if (!(q >= 0.f)) q = 0.f;                      // NaN centres sort first
+        if (q > 1023.f) q = 1023.f;
+        code |= morton10((unsigned)q) << k;
+      }
+      keyed.emplace_back(code, i);
+    }
+    std::sort(keyed.begin(), keyed.end());
+    for (size_t j = 0; j < keyed.size(); ++j) order[j] = keyed[j].second;
+  }
+  return order;
+}
+
+// ---- light grids (large scenes): per light with a NARROW shadow cone (PCF only, sin <= 0.05), the sphere
+// slots binned by where they can occlude, so that a shadow job looks up a handful of spheres instead of
+// scanning every cluster (rt_packet.cuh scan_candidates). Conservative by construction; the job still
+// runs its exact cone test and the exact per-ray tests on every entry, so results do not change.
+//   point / area light at Lp: every ray of a job stays within 1.1*s*t of the axis o + t*L, t <= dist, and
+//     every axis point is seen from the light in direction -L. A sphere (c, r) can be touched only if
+//     the line from Lp along -L passes within R = r + 1.15*s*Dmax of c, i.e. if -L lies within
+//     asin(R / |c - Lp|) of (c - Lp): binned over a cube map of directions around the light (8 x 8 cells
+//     per face); spheres with |c - Lp| <= R go to a list every job reads.
+//   directional light: the same bound around the axis line o + t*L, binned over a 32 x 32 grid of the plane
+//     orthogonal to L (the cell of the origin's projection).
+// Dmax bounds t: jobs farther from the light (point), or starting outside the scene's bounding ball
+// (directional), take the cluster scan. Layout (float4 units from the start of the grid blob):
+//   header, 4 float4 per light: (mode bits, s_grid, bound, first cell bits) (Lp | U, G | umin) (V, vmin) (centre, cells per unit)
+//   offsets: u32 per cell (+ the shared cell + end), all lights back to back;  entries: u16 sphere slots.
+inline float __int_as_float_host(int v) { float f; std::memcpy(&f, &v, 4); return f; }
+struct GridBlob { std::vector<float4> data; int off_f4 = 0, ent_f4 = 0; };
+
+inline int cube_cell(double x, double y, double z, int G) {    // == rt_packet.cuh grid_cube_cell
+  const double ax = std::fabs(x), ay = std::fabs(y), az = std::fabs(z);
+  int face; double a, b;
+  if (ax >= ay && ax >= az) { face = x >= 0 ? 0 : 1; a = y / ax; b = z / ax; }
+  else if (ay >= az)        { face = y >= 0 ? 2 : 3; a = x / ay; b = z / ay; }
+  else                      { face = z >= 0 ? 4 : 5; a = x / az; b = y / az; }
+  int ix = (int)std::floor((a * 0.5 + 0.5) * G), iy = (int)std::floor((b * 0.5 + 0.5) * G);
+  ix = ix < 0 ? 0 : (ix > G - 1 ? G - 1 : ix); iy = iy < 0 ? 0 : (iy > G - 1 ? G - 1 : iy);
+  return (face * G + iy) * G + ix;
+}
+inline void cube_dir(int face, double a, double b, double d[3]) {
+  switch (face) {
+    case 0: d[0] = 1; d[1] = a; d[2] = b; break;
+    case 1: d[0] = -1; d[1] = a; d[2] = b; break;
+    case 2: d[0] = a; d[1] = 1; d[2] = b; break;
+    case 3: d[0] = a; d[1] = -1; d[2] = b; break;
+    case 4: d[0] = a; d[1] = b; d[2] = 1; break;
+    default: d[0] = a; d[1] = b; d[2] = -1; break;
+  }
+  const double inv = 1.0 / std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+  d[0] *= inv; d[1] *= inv; d[2] *= inv;
+}
+
+constexpr int kGridCube = 8, kGridOrtho = 32;
+constexpr float kGridMaxSin = 0.05f;
+
+GridBlob build_light_grids(const rt_object* obj, int n, const rt_light* lights, int m) {
+  GridBlob g;
+  int spheres = 0;
+  for (int i = 0; i < n; ++i) spheres += obj[i].type == 0;
+  if (spheres < rt::kPkClusterMinSpheres || spheres > 65535 || m <= 0 || m > 64) return g;
+  const std::vector<int> order = sphere_slot_order(obj, n, true);
+  // bounding ball of everything a shading point can lie on (spheres and plane rectangles)
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (int i = 0; i < n; ++i) {
+    if (obj[i].type != 0 && obj[i].type != 1) continue;
+    for (int k = 0; k < 3; ++k) {
+      if (!std::isfinite(obj[i].position[k])) return g;
+      lo[k] = std::min(lo[k], (double)obj[i].position[k]); hi[k] = std::max(hi[k], (double)obj[i].position[k]);
+    }
+  }
+  const double ctr[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+  double Rall = 0.0;
+  for (int i = 0; i < n; ++i) {
+    if (obj[i].type != 0 && obj[i].type != 1) continue;
+    const double ext = obj[i].type == 0 ? std::fabs((double)obj[i].radius)
+                                        : 0.5 * std::sqrt((double)obj[i].size[0] * obj[i].size[0] + (double)obj[i].size[1] * obj[i].size[1]);
+    if (!std::isfinite(ext)) return g;
+    const double dx = obj[i].position[0] - ctr[0], dy = obj[i].position[1] - ctr[1], dz = obj[i].position[2] - ctr[2];
+    Rall = std::max(Rall, std::sqrt(dx * dx + dy * dy + dz * dz) + ext);
+  }
+  Rall = Rall * 1.001 + 0.01;                            // + the 0.001 * N offset of a shadow origin
+  // static tables of the cube map: cell centre directions and angular radii
+  static double cdir[6 * kGridCube * kGridCube][3], crad[6 * kGridCube * kGridCube];
+  static bool cube_ready = false;
+  if (!cube_ready) {
+    const int G = kGridCube;
+    for (int f = 0; f < 6; ++f) for (int iy = 0; iy < G; ++iy) for (int ix = 0; ix < G; ++ix) {
+      const int cell = (f * G + iy) * G + ix;
+      const double a = (ix + 0.5) / G * 2 - 1, b = (iy + 0.5) / G * 2 - 1, h = 1.0 / G;
+      cube_dir(f, a, b, cdir[cell]);
+      double worst = 1.0;
+      for (int c4 = 0; c4 < 4; ++c4) {
+        double d[3];
+        cube_dir(f, a + ((c4 & 1) ? h : -h), b + ((c4 & 2) ? h : -h), d);
+        worst = std::min(worst, d[0] * cdir[cell][0] + d[1] * cdir[cell][1] + d[2] * cdir[cell][2]);
+      }
+      crad[cell] = std::acos(std::max(-1.0, std::min(1.0, worst)));
+    }
+    cube_ready = true;
+  }
+  std::vector<float4> hdr((size_t)4 * m, make_float4(0.f, 0.f, 0.f, 0.f));
+  std::vector<unsigned> offsets;
+  std::vector<unsigned short> entries;
+  bool any = false;
+  for (int j = 0; j < m; ++j) {
+    const rt_light& L = lights[j];
+    if (L.shadowType != 1) continue;                     // PCF only: PCSS probes open the cone to tens of degrees
+    const float s_grid = 2.0f * std::fabs(L.shadowSoftness * 0.005f) * 1.01f + 1.0e-5f;   // == Cone::s of such a job
+    if (!(s_grid <= kGridMaxSin)) continue;
+    std::vector<std::vector<unsigned short>> cells;
+    int mode = 0;
+    float4 h1 = make_float4(0, 0, 0, 0), h2 = h1;
+    float bound = 0.f, per_unit = 0.f;
+    if (L.type == 0 || L.type == 2) {
+      const double Lp[3] = {L.position[0], L.position[1], L.position[2]};
+      if (!std::isfinite(Lp[0]) || !std::isfinite(Lp[1]) || !std::isfinite(Lp[2])) continue;
+      const double dl = std::sqrt((Lp[0] - ctr[0]) * (Lp[0] - ctr[0]) + (Lp[1] - ctr[1]) * (Lp[1] - ctr[1]) + (Lp[2] - ctr[2]) * (Lp[2] - ctr[2]));
+      const double Dmax = dl + Rall;
+      const int ncell = 6 * kGridCube * kGridCube;
+      cells.assign(ncell + 1, {});
+      for (int ks = 0; ks < (int)order.size(); ++ks) {
+        const rt_object& o = obj[order[ks]];
+        const double u[3] = {o.position[0] - Lp[0], o.position[1] - Lp[1], o.position[2] - Lp[2]};
+        const double len = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+        const double R = std::fabs((double)o.radius) * 1.001 + 1.15 * s_grid * Dmax + 1e-4 * (len + 1.0);
+        if (!(len > R * 1.01) || !std::isfinite(R)) { cells[ncell].push_back((unsigned short)ks); continue; }
+        const double ang = std::asin(R / len) + 2e-3;
+        for (int c = 0; c < ncell; ++c) {
+          const double lim = std::min(3.14159265358979, ang + crad[c]);
+          if ((u[0] * cdir[c][0] + u[1] * cdir[c][1] + u[2] * cdir[c][2]) >= std::cos(lim) * len) cells[c].push_back((unsigned short)ks);
+        }
+      }
+      mode = 1; bound = (float)(Dmax * 0.999);
+      h1 = make_float4((float)Lp[0], (float)Lp[1], (float)Lp[2], (float)kGridCube);
+    } else if (L.type == 1) {
+      double D[3] = {-(double)L.direction[0], -(double)L.direction[1], -(double)L.direction[2]};   // lightDir = normalize(-direction)
+      const double dn = std::sqrt(D[0] * D[0] + D[1] * D[1] + D[2] * D[2]);
+      if (!(dn > 1e-20) || !std::isfinite(dn)) continue;
+      for (double& v : D) v /= dn;
+      double T[3] = {0, 0, 0};
+      T[std::fabs(D[0]) < 0.6 ? 0 : (std::fabs(D[1]) < 0.6 ? 1 : 2)] = 1.0;
+      double U[3] = {D[1] * T[2] - D[2] * T[1], D[2] * T[0] - D[0] * T[2], D[0] * T[1] - D[1] * T[0]};
+      const double un = std::sqrt(U[0] * U[0] + U[1] * U[1] + U[2] * U[2]);
+      for (double& v : U) v /= un;
+      const double V[3] = {D[1] * U[2] - D[2] * U[1], D[2] * U[0] - D[0] * U[2], D[0] * U[1] - D[1] * U[0]};
+      const double Dmax = 2.1 * Rall, infl = 1.15 * s_grid * Dmax;
+      const double cu = ctr[0] * U[0] + ctr[1] * U[1] + ctr[2] * U[2], cv = ctr[0] * V[0] + ctr[1] * V[1] + ctr[2] * V[2];
+      const double umin = cu - Rall, vmin = cv - Rall, cell = 2.0 * Rall / kGridOrtho;      // origins lie inside the ball
+      const int ncell = kGridOrtho * kGridOrtho;
+      cells.assign(ncell + 1, {});
+      for (int ks = 0; ks < (int)order.size(); ++ks) {
+        const rt_object& o = obj[order[ks]];
+        const double pu = o.position[0] * U[0] + o.position[1] * U[1] + o.position[2] * U[2];
+        const double pv = o.position[0] * V[0] + o.position[1] * V[1] + o.position[2] * V[2];
+        const double R = std::fabs((double)o.radius) * 1.001 + infl + 1e-4 * (Rall + 1.0) + 1e-3 * cell;
+        if (!std::isfinite(R) || !std::isfinite(pu) || !std::isfinite(pv)) { cells[ncell].push_back((unsigned short)ks); continue; }
+        int x0 = (int)std::floor((pu - R - umin) / cell), x1 = (int)std::floor((pu + R - umin) / cell);
+        int y0 = (int)std::floor((pv - R - vmin) / cell), y1 = (int)std::floor((pv + R - vmin) / cell);
+        x0 = std::max(x0, 0); y0 = std::max(y0, 0); x1 = std::min(x1, kGridOrtho - 1); y1 = std::min(y1, kGridOrtho - 1);
+        for (int y = y0; y <= y1; ++y) for (int x = x0; x <= x1; ++x) cells[(size_t)y * kGridOrtho + x].push_back((unsigned short)ks);
+      }
+      mode = 2; bound = (float)(Rall * Rall * 0.998);
+      h1 = make_float4((float)U[0], (float)U[1], (float)U[2], (float)umin);
+      h2 = make_float4((float)V[0], (float)V[1], (float)V[2], (float)vmin);
+      per_unit = (float)(1.0 / cell);
+    } else continue;
+    float4 h0;
+    h0.x = __int_as_float_host(mode); h0.y = s_grid; h0.z = bound; h0.w = __int_as_float_host((int)offsets.size());
+    hdr[4 * j + 0] = h0; hdr[4 * j + 1] = h1; hdr[4 * j + 2] = h2;
+    hdr[4 * j + 3] = make_float4((float)ctr[0], (float)ctr[1], (float)ctr[2], per_unit);
+    for (const auto& cl : cells) { offsets.push_back((unsigned)entries.size()); entries.insert(entries.end(), cl.begin(), cl.end()); }
+    offsets.push_back((unsigned)entries.size());
+    any = true;
+  }
+  if (!any) return g;
+  g.off_f4 = (int)hdr.size();
+  const size_t off_f4s = (offsets.size() * 4 + 15) / 16, ent_f4s = (entries.size() * 2 + 15) / 16 + 1;
+  g.ent_f4 = g.off_f4 + (int)off_f4s;
+  g.data.assign(hdr.size() + off_f4s + ent_f4s, make_float4(0.f, 0.f, 0.f, 0.f));
+  std::memcpy(g.data.data(), hdr.data(), hdr.size() * 16);
+  std::memcpy(g.data.data() + g.off_f4, offsets.data(), offsets.size() * 4);
+  if (!entries.empty()) std::memcpy(g.data.data() + g.ent_f4, entries.data(), entries.size() * 2);
+  return g;
+}
 PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights, int m, float4* out) {
   PkLayout L = {0, 0, 0, 0, 0, 1};
   for (int i = 0; i < n; ++i) {
@@ -192,33 +399,7 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
       r[4 * k + 0] = lo; r[4 * k + 1] = hi; r[4 * k + 2] = hi; r[4 * k + 3] = lo;
     }
   };
-  // slot order of the spheres: array order, or Morton order of the centres when clustered
-  std::vector<int> order;
-  order.reserve(L.spheres);
-  for (int i = 0; i < n; ++i) if (obj[i].type == 0) order.push_back(i);
-  if (L.clusters) {
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    for (int i : order) for (int k = 0; k < 3; ++k) {
-      const float v = obj[i].position[k];
-      if (v < lo[k]) lo[k] = v;
-      if (v > hi[k]) hi[k] = v;
-    }
-    std::vector<std::pair<unsigned, int>> keyed;
-    keyed.reserve(order.size());
-    for (int i : order) {
-      unsigned code = 0;
-      for (int k = 0; k < 3; ++k) {
-        const float ext = hi[k] - lo[k];
-        float q = ext > 0.f ? (obj[i].position[k] - lo[k]) / ext * 1023.f : 0.f;
-        if (!(q >= 0.f)) q = 0.f;                      // NaN centres sort first
-        if (q > 1023.f) q = 1023.f;
-        code |= morton10((unsigned)q) << k;
-      }
-      keyed.emplace_back(code, i);
-    }
-    std::sort(keyed.begin(), keyed.end());
-    for (size_t j = 0; j < keyed.size(); ++j) order[j] = keyed[j].second;
-  }
+  const std::vector<int> order = sphere_slot_order(obj, n, L.clusters > 0);
   for (int ks = 0; ks < L.spheres; ++ks) {
     const rt_object& o = obj[order[ks]];
     float* r = sph + (size_t)ks * 16;
@@ -335,6 +516,7 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if (const char* e2 = getenv("RT_PK_COHERENT")) c->coherent_override = atoi(e2);
   if (const char* e3 = getenv("RT_PK_DENSE")) c->dense_override = atoi(e3);
   if (const char* e4 = getenv("RT_PK_FAN")) c->fan_override = atoi(e4);
+  if (const char* e5 = getenv("RT_PK_GRID")) c->grid_override = atoi(e5);
   *out = c;
   return RT_OK;
 }
@@ -370,7 +552,25 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
   const size_t off_plane = (size_t)3 * n, off_material = off_plane + (size_t)3 * planes;
   const size_t off_lights = off_material + (size_t)4 * n, off_pk = off_lights + (size_t)6 * m;
   const PkLayout pkl = stage_scene_packet(obj, n, (const rt_light*)lights, m, nullptr);
-  const size_t total = off_pk + pkl.float4s;
+  // light grids of large scenes, rebuilt only when the bytes change
+  if (pkl.clusters > 0 && c->grid_override != 0) {
+    const size_t ob = (size_t)n * sizeof(rt_object), lb = (size_t)m * sizeof(rt_light);
+    const bool same = c->grid_key.size() == ob + lb + 8 && std::memcmp(c->grid_key.data() + 8, objects, ob) == 0 &&
+                      (lb == 0 || std::memcmp(c->grid_key.data() + 8 + ob, lights, lb) == 0) &&
+                      std::memcmp(c->grid_key.data(), &n, 4) == 0 && std::memcmp(c->grid_key.data() + 4, &m, 4) == 0;
+    if (!same) {
+      GridBlob g = build_light_grids(obj, n, (const rt_light*)lights, m);
+      c->grid_data.swap(g.data); c->grid_off_f4 = g.off_f4; c->grid_ent_f4 = g.ent_f4;
+      c->grid_key.resize(ob + lb + 8);
+      std::memcpy(c->grid_key.data(), &n, 4); std::memcpy(c->grid_key.data() + 4, &m, 4);
+      if (ob) std::memcpy(c->grid_key.data() + 8, objects, ob);
+      if (lb) std::memcpy(c->grid_key.data() + 8 + ob, lights, lb);
+    }
+  } else {
+    c->grid_data.clear(); c->grid_key.clear();
+  }
+  const size_t off_grid = off_pk + pkl.float4s;
+  const size_t total = off_grid + c->grid_data.size();
   const size_t need = (total > 0 ? total : 1) * sizeof(float4);
   if (c->stage_pending) { RT_CUDA(c, cudaEventSynchronize(c->stage_done)); c->stage_pending = false; }
   if (need > c->h_stage_cap) {
@@ -387,6 +587,8 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
   }
   stage_scene(obj, n, (const rt_light*)lights, m, planes, c->h_stage, off_plane, off_material, off_lights);
   if (pkl.float4s) stage_scene_packet(obj, n, (const rt_light*)lights, m, c->h_stage + off_pk);
+  if (!c->grid_data.empty()) std::memcpy(c->h_stage + off_grid, c->grid_data.data(), c->grid_data.size() * sizeof(float4));
+  c->off_grid = off_grid; c->grid_f4s = c->grid_data.size();
   RT_CUDA(c, cudaMemcpyAsync(c->d_scene, c->h_stage, total * sizeof(float4), cudaMemcpyHostToDevice, stream));
   c->n_obj = n; c->n_planes = planes; c->n_lights = m;
   c->off_plane = off_plane; c->off_material = off_material; c->off_lights = off_lights;
@@ -514,6 +716,7 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   sc.pk_num_clusters = c->pk_clusters;
+  sc.pk_grid = c->grid_f4s ? c->d_scene + c->off_grid : nullptr; sc.pk_grid_off_f4 = c->grid_off_f4; sc.pk_grid_ent_f4 = c->grid_ent_f4;
   sc.pk_fan_ok = c->fan_override >= 0 ? (c->fan_override && c->pk_fan_ok) : c->pk_fan_ok;
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);
   // with long loops the barrier imbalance costs more than the fetch locality gains.

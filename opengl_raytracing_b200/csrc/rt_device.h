@@ -55,6 +55,8 @@ struct DeviceScene {
   int pk_lights_offset;      // bytes from the start of the blob
   int pk_big;                // 1: large-scene kernel (independent warps, two-level boxes)
   int pk_coherent;           // 1: CTA-coherent phases (small scenes), 0: independent warps
+  const float4* pk_grid;     // light grids of large scenes (rt_abi.cu build_light_grids), nullptr = none; global memory
+  int pk_grid_off_f4, pk_grid_ent_f4;   // float4 offsets of the cell-offset (u32) and entry (u16) arrays inside pk_grid
   int pk_fan_ok;             // 1: every sphere's box contains its sphere (analytic PCSS probe classification allowed)
   int pk_dense;              // large-scene kernel only: 1 = the 80-register build (3 CTAs / 24 warps per SM), 0 = 128 registers (2 / 16)
 };

@@ -100,6 +100,8 @@ struct Scene {
   const float4* material;     // global memory, 4 float4 per ORIGINAL object index
   int nc, ns, np, nl;
   float maxd;
+  const float4* grid;         // global memory: light grids (rt_abi.cu build_light_grids), nullptr = none
+  int grid_off_f4, grid_ent_f4;
 };
 
 __device__ __forceinline__ float lds32(saddr p) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(p)); return v; }
@@ -358,13 +360,69 @@ __device__ __forceinline__ saddr record_of(const Scene& s, int code) {
 }
 __device__ __forceinline__ int cand_code(const Cands& cd, int i) { return cd.list ? cand_load(cd.base, i) : i; }
 
+// Cell of the light grid a job reads (rt_abi.cu build_light_grids holds the derivation and the layout),
+// or -1 when the job is not covered: no grid for this light, a wider cone than the grid was inflated for,
+// an origin farther from the light / outside the scene ball than the bound the grid assumes (NaN: -1).
+__device__ __forceinline__ int grid_cell(const Scene& s, int light_index, const Cone& cone, f3 o, float lightDistance, int& first_cell, int& shared_cell) {
+  const float4 h0 = __ldg(s.grid + 4 * light_index);
+  const int mode = __float_as_int(h0.x);
+  if (mode == 0 || !(cone.s <= h0.y)) return -1;
+  first_cell = __float_as_int(h0.w);
+  const float4 h1 = __ldg(s.grid + 4 * light_index + 1);
+  if (mode == 1) {                                           // cube map of directions around the light: look up -L
+    if (!(lightDistance <= h0.z)) return -1;
+    const int G = (int)h1.w;
+    shared_cell = 6 * G * G;
+    const float x = -cone.L.x, y = -cone.L.y, z = -cone.L.z;
+    const float ax = fabsf(x), ay = fabsf(y), az = fabsf(z);
+    int face; float a, b, m;
+    if (ax >= ay && ax >= az) { face = x >= 0.0f ? 0 : 1; a = y; b = z; m = ax; }
+    else if (ay >= az)        { face = y >= 0.0f ? 2 : 3; a = x; b = z; m = ay; }
+    else                      { face = z >= 0.0f ? 4 : 5; a = x; b = y; m = az; }
+    if (!(m > 0.0f)) return -1;
+    const float inv = __fdividef(0.5f * (float)G, m), hg = 0.5f * (float)G;
+    int ix = (int)floorf(fmaf(a, inv, hg)), iy = (int)floorf(fmaf(b, inv, hg));
+    ix = min(max(ix, 0), G - 1); iy = min(max(iy, 0), G - 1);
+    return (face * G + iy) * G + ix;
+  }
+  const float4 h2 = __ldg(s.grid + 4 * light_index + 2), h3 = __ldg(s.grid + 4 * light_index + 3);
+  const f3 v = o - xyz(h3);                                  // orthographic grid: the origin's projection
+  if (!(fmaf(v.z, v.z, fmaf(v.y, v.y, v.x * v.x)) <= h0.z)) return -1;
+  constexpr int G = 32;
+  shared_cell = G * G;
+  const float ou = fmaf(o.z, h1.z, fmaf(o.y, h1.y, o.x * h1.x)), ov = fmaf(o.z, h2.z, fmaf(o.y, h2.y, o.x * h2.x));
+  int ix = (int)floorf((ou - h1.w) * h3.w), iy = (int)floorf((ov - h2.w) * h3.w);
+  ix = min(max(ix, 0), G - 1); iy = min(max(iy, 0), G - 1);
+  return iy * G + ix;
+}
+
 // One scan of the scene per shadow job. Returns the candidate set for the job's packets.
 template <bool BIG>
-__device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base, bool cone_ok, const Cone& cone, f3 o) {
+__device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base, bool cone_ok, const Cone& cone, f3 o,
+                                                 int light_index, float lightDistance) {
   Cands cd; cd.base = cand_base; cd.n = s.ns + s.np; cd.first = 0; cd.nsph = s.ns; cd.list = false; cd.prefilter = false;
   if (!cone_ok) return cd;
   int n = 0;
-  if (BIG && s.nc > 0) {                                     // cluster bounding spheres first, then members
+  int first_cell = 0, shared_cell = 0;
+  const int cell = (BIG && s.grid) ? grid_cell(s, light_index, cone, o, lightDistance, first_cell, shared_cell) : -1;
+  if (BIG && cell >= 0) {                                    // light grid: the cell's spheres + the shared list, exact cone test on each
+    const unsigned* offs = reinterpret_cast<const unsigned*>(s.grid + s.grid_off_f4) + first_cell;
+    const unsigned short* ents = reinterpret_cast<const unsigned short*>(s.grid + s.grid_ent_f4);
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      const int cidx = pass ? shared_cell : cell;
+      const unsigned e0 = __ldg(offs + cidx), e1 = __ldg(offs + cidx + 1);
+#pragma unroll 1
+      for (unsigned e = e0; e < e1; ++e) {
+        const int k = (int)__ldg(ents + e);
+        const float4 sp = lds128(s.sph + (unsigned)k * kSphereBytes + 48u);
+        PK_STAT(4, 1);
+        if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
+        if (n < kCandCap) cand_store(cand_base, n, k);
+        ++n;
+      }
+    }
+  } else if (BIG && s.nc > 0) {                              // cluster bounding spheres first, then members
     saddr crec = s.clu;
 #pragma unroll 1
     for (int c = 0; c < s.nc; ++c, crec += kSphereBytes) {
@@ -583,7 +641,7 @@ __device__ __noinline__ int probe_fan(saddr sph, saddr cand_base, int nsph, f3 o
 // samples run through ONE packet site: jobs [0,nprobe) are probes, [nprobe,nprobe+pcf) samples.
 template <bool BIG, bool FAN>
 __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
-                                                f3 lightDir, float lightDistance) {
+                                                int light_index, f3 lightDir, float lightDistance) {
   const int nprobe = light.shadowType == 2 ? 16 : 0;
   const int total = nprobe + (light.pcfSamples > 0 ? light.pcfSamples : 0);
   const float filterSize = light.shadowSoftness * 0.005f;                        // glsl:364 (overwrites :352)
@@ -609,7 +667,7 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   }
   const float ll = dot3(lightDir, lightDir);
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
-  const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin);
+  const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin, light_index, lightDistance);
   if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
   // (the frame only steers shadow rays: single-MUFU normalisation in the fast build; 0 * inf is NaN in both)
   const f3 tangent = normalize_shadow(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
@@ -781,7 +839,7 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     if (brdf.x == 0.0f && brdf.y == 0.0f && brdf.z == 0.0f && (!sampled || light.pcfSamples > 0)) continue;
     float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
     if (light.shadowType == 0) shadowFactor = 1.0f;
-    else if (sampled) shadowFactor = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, lightDir, lightDistance);
+    else if (sampled) shadowFactor = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, i, lightDir, lightDistance);
     Lo = smad3(brdf, shadowFactor, Lo);
   }
   if (lit && mat.subsurfaceScatter > 0.0f) {
@@ -929,6 +987,7 @@ __global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_ke
   s.material = sc.material;
   s.nc = BIG ? sc.pk_num_clusters : 0; s.ns = sc.pk_num_spheres; s.np = sc.pk_num_planes; s.nl = sc.num_lights;
   s.maxd = fp.max_ray_distance;
+  s.grid = BIG ? sc.pk_grid : nullptr; s.grid_off_f4 = sc.pk_grid_off_f4; s.grid_ent_f4 = sc.pk_grid_ent_f4;
   // per-thread candidate list behind the scene image: entry i of thread t at +(i*kThreads + t)*2
   const saddr cand_base = base + (unsigned)sc.pk_float4s * 16u + threadIdx.x * 2u;
 

@@ -142,6 +142,36 @@ def test_analytic_probe_classification_matches_exact_probes(monkeypatch, n, size
     monkeypatch.delenv("RT_PK_FAN")
 
 
+@pytest.mark.parametrize("case", ["C3", "C5", "light_inside", "wide_and_narrow"])
+def test_light_grids_do_not_change_the_image(monkeypatch, case):
+    """Large scenes: shadow jobs of narrow-cone (PCF) lights read their candidate spheres from a
+    per-light grid (cube map of directions around a point / area light, orthographic grid for a
+    directional light; rt_abi.cu build_light_grids) instead of scanning the clusters. The grid is
+    conservative and every entry still goes through the exact tests, so the image must be the
+    one of the cluster scan (RT_PK_GRID=0) bit for bit, in both math builds."""
+    from opengl_raytracing_b200.pipeline import RtContext
+    if case == "C3":
+        w = synthetic.config(3, 640, 360)
+    else:
+        w = synthetic.config(5, 960, 540)
+        if case == "light_inside":                 # a point light in the middle of the sphere field: the shared list is used
+            w.lights["position"][1] = (0.5, 0.2, -30.0)
+            w.lights["intensity"][1] = 30.0
+        elif case == "wide_and_narrow":            # softness just below / above the grid's cone limit (sin 0.05)
+            w.lights["shadowSoftness"][0] = 4.9
+            w.lights["shadowSoftness"][1] = 5.1
+            w.lights["pcfSamples"][1] = 7
+    for fl in (abi.FLAG_NORMAL_FP32, abi.FLAG_NORMAL_FP32 | abi.FLAG_PARITY_MATH):
+        outs = {}
+        for grid in ("0", "1"):
+            monkeypatch.setenv("RT_PK_GRID", grid)
+            c = RtContext(0)
+            outs[grid] = render_workload(c, w, flags=fl)
+            c.close()
+        assert _bits_equal(outs["0"], outs["1"]) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}, (case, fl)
+    monkeypatch.delenv("RT_PK_GRID")
+
+
 def test_fast_packet_kernel_stays_close_to_fast_literal_kernel(rt_ctx):
     """Fast build: the packet kernel additionally approximates shadow-ray setup (MUFU rcp/rsqrt,
     root-free sphere occlusion). Those can only flip a shadow sample at an exact silhouette."""
