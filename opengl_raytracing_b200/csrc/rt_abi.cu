@@ -251,25 +251,27 @@ GridBlob build_light_grids(const rt_object* obj, int n, const rt_light* lights, 
     Rall = std::max(Rall, std::sqrt(dx * dx + dy * dy + dz * dz) + ext);
   }
   Rall = Rall * 1.001 + 0.01;                            // + the 0.001 * N offset of a shadow origin
-  // static tables of the cube map: cell centre directions and angular radii
-  static double cdir[6 * kGridCube * kGridCube][3], crad[6 * kGridCube * kGridCube];
-  static bool cube_ready = false;
-  if (!cube_ready) {
+  // static tables of the cube map: cell centre directions and angular radii (initialised once, thread-safe)
+  struct CubeTables { double dir[6 * kGridCube * kGridCube][3]; double rad[6 * kGridCube * kGridCube]; };
+  static const CubeTables* const tables = [] {
+    CubeTables* t = new CubeTables;
     const int G = kGridCube;
     for (int f = 0; f < 6; ++f) for (int iy = 0; iy < G; ++iy) for (int ix = 0; ix < G; ++ix) {
       const int cell = (f * G + iy) * G + ix;
       const double a = (ix + 0.5) / G * 2 - 1, b = (iy + 0.5) / G * 2 - 1, h = 1.0 / G;
-      cube_dir(f, a, b, cdir[cell]);
+      cube_dir(f, a, b, t->dir[cell]);
       double worst = 1.0;
       for (int c4 = 0; c4 < 4; ++c4) {
         double d[3];
         cube_dir(f, a + ((c4 & 1) ? h : -h), b + ((c4 & 2) ? h : -h), d);
-        worst = std::min(worst, d[0] * cdir[cell][0] + d[1] * cdir[cell][1] + d[2] * cdir[cell][2]);
+        worst = std::min(worst, d[0] * t->dir[cell][0] + d[1] * t->dir[cell][1] + d[2] * t->dir[cell][2]);
       }
-      crad[cell] = std::acos(std::max(-1.0, std::min(1.0, worst)));
+      t->rad[cell] = std::acos(std::max(-1.0, std::min(1.0, worst)));
     }
-    cube_ready = true;
-  }
+    return t;
+  }();
+  const double (*cdir)[3] = tables->dir;
+  const double* crad = tables->rad;
   std::vector<float4> hdr((size_t)4 * m, make_float4(0.f, 0.f, 0.f, 0.f));
   std::vector<unsigned> offsets;
   std::vector<unsigned short> entries;
@@ -297,9 +299,14 @@ GridBlob build_light_grids(const rt_object* obj, int n, const rt_light* lights, 
         const double R = std::fabs((double)o.radius) * 1.001 + 1.15 * s_grid * Dmax + 1e-4 * (len + 1.0);
         if (!(len > R * 1.01) || !std::isfinite(R)) { cells[ncell].push_back((unsigned short)ks); continue; }
         const double ang = std::asin(R / len) + 2e-3;
-        for (int c = 0; c < ncell; ++c) {
-          const double lim = std::min(3.14159265358979, ang + crad[c]);
-          if ((u[0] * cdir[c][0] + u[1] * cdir[c][1] + u[2] * cdir[c][2]) >= std::cos(lim) * len) cells[c].push_back((unsigned short)ks);
+        for (int f = 0; f < 6; ++f) {
+          // a face spans 54.74 degrees around its axis: skip the faces the sphere's disc cannot reach
+          const double axis_dot = (f & 1 ? -1.0 : 1.0) * u[f >> 1];
+          if (axis_dot < std::cos(std::min(3.14159265358979, ang + 0.9554)) * len) continue;
+          for (int c = f * kGridCube * kGridCube; c < (f + 1) * kGridCube * kGridCube; ++c) {
+            const double lim = std::min(3.14159265358979, ang + crad[c]);
+            if ((u[0] * cdir[c][0] + u[1] * cdir[c][1] + u[2] * cdir[c][2]) >= std::cos(lim) * len) cells[c].push_back((unsigned short)ks);
+          }
         }
       }
       mode = 1; bound = (float)(Dmax * 0.999);
