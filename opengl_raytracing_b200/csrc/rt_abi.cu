@@ -279,7 +279,8 @@ GridBlob build_light_grids(const rt_object* obj, int n, const rt_light* lights, 
   for (int j = 0; j < m; ++j) {
     const rt_light& L = lights[j];
     if (L.shadowType != 1) continue;                     // PCF only: PCSS probes open the cone to tens of degrees
-    const float s_grid = 2.0f * std::fabs(L.shadowSoftness * 0.005f) * 1.01f + 1.0e-5f;   // == Cone::s of such a job
+    // Cone::s of such a job (rt_packet.cuh shadow_packets), a hair wider so that the device's `cone.s <= s_grid` holds whatever the last ulp
+    const float s_grid = (2.0f * std::fabs(L.shadowSoftness * 0.005f) * 1.01f + 1.0e-5f) * 1.0001f;
     if (!(s_grid <= kGridMaxSin)) continue;
     std::vector<std::vector<unsigned short>> cells;
     int mode = 0;
