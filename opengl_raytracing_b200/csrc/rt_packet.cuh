@@ -499,7 +499,7 @@ __device__ __noinline__ bool trace_any_one(const Scene& s, const Cands& cd, cons
 // axis); a ray with a NaN direction cannot hit anything (every comparison is false); a ray with a
 // zero / denormal / infinite component goes through the generic single-ray routine.
 __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands& cd, const Cone& cone, f3 o,
-                                                     const f3 (&d)[4], unsigned active, float lim) {
+                                                     const f3 (&d)[4], unsigned active, float lim, unsigned usign) {
   float a[4], m4a[4], m2al[4];
   float2 ivx[4], ivy[4], ivz[4];
   unsigned signs = 0u, remaining = active, occ = 0u;       // signs: 3 bits per ray
@@ -507,13 +507,19 @@ __device__ __forceinline__ unsigned trace_any_packet(const Scene& s, const Cands
   for (int r = 0; r < 4; ++r) {
     a[r] = sdot3(d[r], d[r]);
     m4a[r] = -4.0f * a[r]; m2al[r] = -2.0f * a[r] * lim;
-    signs |= ((__float_as_uint(d[r].x) >> 31) | ((__float_as_uint(d[r].y) >> 31) << 1) | ((__float_as_uint(d[r].z) >> 31) << 2)) << (3 * r);
     ivx[r] = dup2(rcp_shadow(d[r].x)); ivy[r] = dup2(rcp_shadow(d[r].y)); ivz[r] = dup2(rcp_shadow(d[r].z));   // FMUL2 takes the scalar broadcast form
-    if (((active >> r) & 1u) && !dir_regular(d[r], a[r])) {
-      remaining &= ~(1u << r);
-      if (a[r] == a[r]) {                                                               // a is NaN iff a component is
-        const Scene s2 = s; const Cands cd2 = cd; const Cone cone2 = cone;              // copies: see trace_closest
-        if (trace_any_one(s2, cd2, cone2, o, d[r], lim)) occ |= 1u << r;
+  }
+  if (usign < 8u) signs = usign * 0x249u;                  // the job proved every ray regular, with these signs (shadow_packets)
+  else {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      signs |= ((__float_as_uint(d[r].x) >> 31) | ((__float_as_uint(d[r].y) >> 31) << 1) | ((__float_as_uint(d[r].z) >> 31) << 2)) << (3 * r);
+      if (((active >> r) & 1u) && !dir_regular(d[r], a[r])) {
+        remaining &= ~(1u << r);
+        if (a[r] == a[r]) {                                                             // a is NaN iff a component is
+          const Scene s2 = s; const Cands cd2 = cd; const Cone cone2 = cone;            // copies: see trace_closest
+          if (trace_any_one(s2, cd2, cone2, o, d[r], lim)) occ |= 1u << r;
+        }
       }
     }
   }
@@ -669,12 +675,6 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
   const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin, light_index, lightDistance);
   if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
-  // (the frame only steers shadow rays: single-MUFU normalisation in the fast build; 0 * inf is NaN in both)
-  const f3 tangent = normalize_shadow(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
-  const f3 bitangent = cross3(lightDir, tangent);
-#if !RT_PARITY
-  const f3 tangent_fs = tangent * filterSize, bitangent_fs = bitangent * filterSize;
-#endif
   int unoccluded = 0;
   int j = 0;
   int probe_first = 0;                                   // exact probe packets visit candidates [probe_first, n)
@@ -688,6 +688,18 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
     }
   }
 #endif
+  // (the frame only steers shadow rays: single-MUFU normalisation in the fast build; 0 * inf is NaN in both)
+  const f3 tangent = normalize_shadow(cross3(lightDir, mk3(0.0f, 1.0f, 0.0f)));   // NaN when lightDir || Y (glsl:349)
+  const f3 bitangent = cross3(lightDir, tangent);
+#if !RT_PARITY
+  const f3 tangent_fs = tangent * filterSize, bitangent_fs = bitangent * filterSize;
+#endif
+  // Every ray of the job is lightDir + delta with |delta_i| <= e <= cone.s per component (glsl:371-378, :409;
+  // normalising scales by a positive number): when every |lightDir_i| clears that bound, all rays are
+  // regular and share lightDir's signs, and the packets skip their per-ray sign / regularity bookkeeping.
+  unsigned usign = 8u;                                   // 8: not proven uniform
+  if (cone_ok && fmin3(fabsf(lightDir.x), fabsf(lightDir.y), fabsf(lightDir.z)) > cone.s * 1.05f + 1.0e-6f)
+    usign = (__float_as_uint(lightDir.x) >> 31) | ((__float_as_uint(lightDir.y) >> 31) << 1) | ((__float_as_uint(lightDir.z) >> 31) << 2);
   while (j < total) {
     const bool probing = j < nprobe;
     const int end = probing ? nprobe : total;
@@ -719,7 +731,7 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
     }
     Cands cdj = cd;
     if (FAN) cdj.first = probing ? probe_first : 0;
-    const unsigned occ = trace_any_packet(s, cdj, cone, origin, d, active, probing ? lim_probe : lim_pcf) & active;
+    const unsigned occ = trace_any_packet(s, cdj, cone, origin, d, active, probing ? lim_probe : lim_pcf, usign) & active;
     if (probing) {
       if (occ) { j = nprobe; continue; }                 // a blocker exists: go to the PCF phase
       j += 4;
