@@ -273,6 +273,16 @@ rt_status rt_measure_fp32_peak(rt_context* ctx, double* tflops, int* sm_count, d
 /* Device kernel launch counter (every kernel this library launched on ctx). */
 uint64_t  rt_launch_count(rt_context* ctx);
 
+/* Introspection of the host-side scene staging (no CUDA call, no context): builds the light grids
+ * rt_upload_scene would build for these records (large scenes only) into
+ * `out` (16-byte units) and returns how many units the blob has (0 = no grid for this scene); when
+ * `capacity_f4` is too small nothing is written. Layout: 4 units of header per light, then the u32
+ * cell offsets at unit *off_f4, then the u16 sphere-slot entries at unit *ent_f4; `slot_to_object`
+ * (n ints, may be NULL) receives the original object index of every sphere slot. Used by the CPU
+ * tests to check that the grids are conservative.                                              */
+size_t    rt_debug_light_grids(const void* objects, int n, const void* lights, int m, void* out, size_t capacity_f4,
+                               int* off_f4, int* ent_f4, int* slot_to_object);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,6 +35,7 @@ EXPORTED_SYMBOLS = [
     "rt_set_skybox", "rt_set_noise", "rt_render", "rt_render_host", "rt_synchronize", "rt_render_gl",
     "rt_get_counters", "rt_set_host_path", "rt_device_alloc", "rt_device_free", "rt_ipc_export",
     "rt_ipc_open", "rt_ipc_close", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
+    "rt_debug_light_grids",
 ]
 POST_EXPORTED_SYMBOLS = [                   # include/rt_post.h
     "rt_generate_aabbs", "rt_generate_aabbs_device", "rt_decode_rgbe", "rt_equirect_to_cubemap",
@@ -134,6 +135,8 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(ip), C.POINTER(C.c_double)]
     lib.rt_launch_count.argtypes = [vp]
     lib.rt_launch_count.restype = C.c_uint64
+    lib.rt_debug_light_grids.argtypes = [vp, ip, vp, ip, vp, C.c_size_t, C.POINTER(ip), C.POINTER(ip), vp]
+    lib.rt_debug_light_grids.restype = C.c_size_t
     # include/rt_post.h
     pp = C.POINTER(PostParams)
     lib.rt_generate_aabbs.argtypes = [vp, vp, ip]

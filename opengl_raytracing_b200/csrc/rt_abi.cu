@@ -949,4 +949,19 @@ rt_status rt_measure_fp32_peak(rt_context* c, double* tflops, int* sm_count, dou
 
 uint64_t rt_launch_count(rt_context* c) { return c ? c->launches : 0; }
 
+size_t rt_debug_light_grids(const void* objects, int n, const void* lights, int m, void* out, size_t capacity_f4,
+                            int* off_f4, int* ent_f4, int* slot_to_object) {
+  if (n < 0 || m < 0 || (n > 0 && !objects) || (m > 0 && !lights)) return 0;
+  const rt_object* obj = (const rt_object*)objects;
+  const GridBlob g = build_light_grids(obj, n, (const rt_light*)lights, m);
+  if (off_f4) *off_f4 = g.off_f4;
+  if (ent_f4) *ent_f4 = g.ent_f4;
+  if (slot_to_object) {
+    const std::vector<int> order = sphere_slot_order(obj, n, true);
+    for (size_t k = 0; k < order.size(); ++k) slot_to_object[k] = order[k];
+  }
+  if (out && g.data.size() <= capacity_f4 && !g.data.empty()) std::memcpy(out, g.data.data(), g.data.size() * sizeof(float4));
+  return g.data.size();
+}
+
 }  // extern "C"
