@@ -31,7 +31,7 @@ struct rt_context {
   int n_obj = 0, n_planes = 0, n_lights = 0;
   size_t off_plane = 0, off_material = 0, off_lights = 0;   // in float4 units
   // packet-kernel blob (appended to the same device buffer)
-  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0, pk_clusters = 0, pk_fan_ok = 0;
+  size_t off_pk = 0, pk_float4s = 0; int pk_spheres = 0, pk_planes = 0, pk_lights_offset = 0, pk_clusters = 0, pk_fan_ok = 0, pk_material_offset = -1;
   // textures
   uint2* d_sky = nullptr; cudaArray_t sky_array = nullptr; cudaTextureObject_t sky_tex = 0; int sky_size = 0;
   unsigned char* d_noise = nullptr; int noise_w = 0, noise_h = 0;
@@ -140,7 +140,7 @@ void stage_scene(const rt_object* obj, int n, const rt_light* lights, int m, int
 // Object[]/Light[] -> the packet kernel's shared-memory image (layout in rt_packet.cuh).
 // Returns the size in float4 units, or 0 when the scene cannot use the sign-select loops
 // (a non-finite bound). `out` may be null to size only.
-struct PkLayout { size_t float4s; int spheres, planes, lights_offset, clusters, fan_ok; };
+struct PkLayout { size_t float4s; int spheres, planes, lights_offset, clusters, fan_ok, material_offset; };
 
 inline unsigned morton10(unsigned v) {                   // spread 10 bits to every third position
   v &= 1023u;
@@ -363,12 +363,12 @@ GridBlob build_light_grids(const rt_object* obj, int n, const rt_light* lights, 
   return g;
 }
 PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights, int m, float4* out) {
-  PkLayout L = {0, 0, 0, 0, 0, 1};
+  PkLayout L = {0, 0, 0, 0, 0, 1, -1};
   for (int i = 0; i < n; ++i) {
     if (obj[i].type == 0) L.spheres++; else if (obj[i].type == 1) L.planes++;
     if (obj[i].type == 0 || obj[i].type == 1)
       for (int k = 0; k < 3; ++k)
-        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0, 0, 0};
+        if (!std::isfinite(obj[i].bounds.min[k]) || !std::isfinite(obj[i].bounds.max[k])) return PkLayout{0, 0, 0, 0, 0, 0, -1};
     // fan_ok: every sphere's box contains the sphere (what GenerateAABBForObject produces). The
     // fast build's analytic PCSS probe classification (rt_packet.cuh probe_fan) relies on "a ray
     // that hits the sphere with margin also passes its box"; any other box sends probes down the
@@ -391,6 +391,9 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
   bytes = (bytes + 15) / 16 * 16;
   L.lights_offset = (int)bytes;
   bytes += (size_t)m * sizeof(rt_light);
+  // small scenes: the material records (4 float4 per ORIGINAL object index, as stage_scene lays them out)
+  // ride in the shared-memory blob too, so a closest hit reads them with LDS instead of 4 global loads
+  if (L.spheres + L.planes <= 48 && n <= 64) { L.material_offset = (int)bytes; bytes += (size_t)n * 64; }
   L.float4s = bytes / 16;
   if (L.float4s == 0) L.float4s = 1;
   if (!out) return L;
@@ -456,6 +459,16 @@ PkLayout stage_scene_packet(const rt_object* obj, int n, const rt_light* lights,
     kp++;
   }
   if (m > 0) std::memcpy(base + L.lights_offset, lights, (size_t)m * sizeof(rt_light));
+  if (L.material_offset >= 0) {
+    float4* mat = (float4*)(base + L.material_offset);
+    for (int i = 0; i < n; ++i) {
+      const rt_material& a = obj[i].material;
+      mat[4 * i + 0] = make_float4(a.albedo[0], a.albedo[1], a.albedo[2], a.metallic);
+      mat[4 * i + 1] = make_float4(a.roughness, a.diffuseStrength, a.ior, a.transparency);
+      mat[4 * i + 2] = make_float4(a.subsurfaceColor[0], a.subsurfaceColor[1], a.subsurfaceColor[2], a.subsurfaceScatter);
+      mat[4 * i + 3] = make_float4(a.scatterDistance, 0.f, 0.f, 0.f);
+    }
+  }
   return L;
 }
 
@@ -601,7 +614,7 @@ rt_status rt_upload_scene(rt_context* c, const void* objects, int n, const void*
   c->n_obj = n; c->n_planes = planes; c->n_lights = m;
   c->off_plane = off_plane; c->off_material = off_material; c->off_lights = off_lights;
   c->off_pk = off_pk; c->pk_float4s = pkl.float4s; c->pk_spheres = pkl.spheres; c->pk_planes = pkl.planes;
-  c->pk_lights_offset = pkl.lights_offset; c->pk_clusters = pkl.clusters;
+  c->pk_lights_offset = pkl.lights_offset; c->pk_clusters = pkl.clusters; c->pk_material_offset = pkl.material_offset;
   bool has_pcss = false;                                 // the analytic probe path only pays where a PCSS light exists
   for (int j = 0; j < m; ++j) has_pcss = has_pcss || ((const rt_light*)lights)[j].shadowType == 2;
   c->pk_fan_ok = (pkl.fan_ok && has_pcss) ? 1 : 0;
@@ -724,6 +737,7 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   sc.pk_num_clusters = c->pk_clusters;
+  sc.pk_material_offset = c->pk_material_offset;
   sc.pk_grid = c->grid_f4s ? c->d_scene + c->off_grid : nullptr; sc.pk_grid_off_f4 = c->grid_off_f4; sc.pk_grid_ent_f4 = c->grid_ent_f4;
   sc.pk_fan_ok = c->fan_override >= 0 ? (c->fan_override && c->pk_fan_ok) : c->pk_fan_ok;
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);

@@ -53,6 +53,7 @@ struct DeviceScene {
   int pk_num_spheres, pk_num_planes;
   int pk_num_clusters;       // 0: no cluster level (fewer than kPkClusterMinSpheres spheres)
   int pk_lights_offset;      // bytes from the start of the blob
+  int pk_material_offset;    // bytes from the start of the blob to the material records (small scenes), -1 = not in the blob
   int pk_big;                // 1: large-scene kernel (independent warps, two-level boxes)
   int pk_coherent;           // 1: CTA-coherent phases (small scenes), 0: independent warps
   const float4* pk_grid;     // light grids of large scenes (rt_abi.cu build_light_grids), nullptr = none; global memory

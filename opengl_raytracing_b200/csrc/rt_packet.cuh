@@ -98,6 +98,7 @@ struct Scene {
   saddr sph_index;            // shared memory
   saddr lights;               // shared memory, raw 96-B records
   const float4* material;     // global memory, 4 float4 per ORIGINAL object index
+  saddr material_smem;        // the same records inside the shared-memory blob (small scenes), 0 = not staged
   int nc, ns, np, nl;
   float maxd;
   const float4* grid;         // global memory: light grids (rt_abi.cu build_light_grids), nullptr = none
@@ -586,8 +587,14 @@ __device__ __forceinline__ LightRec load_light(const Scene& s, int i) {
   return r;
 }
 __device__ __forceinline__ Mat load_material(const Scene& s, int index) {
-  const float4 m0 = __ldg(s.material + 4 * index + 0), m1 = __ldg(s.material + 4 * index + 1);
-  const float4 m2 = __ldg(s.material + 4 * index + 2), m3 = __ldg(s.material + 4 * index + 3);
+  float4 m0, m1, m2, m3;
+  if (s.material_smem) {
+    const saddr a = s.material_smem + (unsigned)index * 64u;
+    m0 = lds128(a); m1 = lds128(a + 16u); m2 = lds128(a + 32u); m3 = lds128(a + 48u);
+  } else {
+    m0 = __ldg(s.material + 4 * index + 0); m1 = __ldg(s.material + 4 * index + 1);
+    m2 = __ldg(s.material + 4 * index + 2); m3 = __ldg(s.material + 4 * index + 3);
+  }
   Mat m;
   m.albedo = xyz(m0); m.metallic = m0.w;
   m.roughness = m1.x; m.diffuseStrength = m1.y; m.ior = m1.z; m.transparency = m1.w;
@@ -997,6 +1004,7 @@ __global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_ke
   s.sph_index = s.pln + (unsigned)sc.pk_num_planes * kPlaneBytes;
   s.lights = base + (unsigned)sc.pk_lights_offset;
   s.material = sc.material;
+  s.material_smem = (!BIG && sc.pk_material_offset >= 0) ? base + (unsigned)sc.pk_material_offset : 0u;
   s.nc = BIG ? sc.pk_num_clusters : 0; s.ns = sc.pk_num_spheres; s.np = sc.pk_num_planes; s.nl = sc.num_lights;
   s.maxd = fp.max_ray_distance;
   s.grid = BIG ? sc.pk_grid : nullptr; s.grid_off_f4 = sc.pk_grid_off_f4; s.grid_ent_f4 = sc.pk_grid_ent_f4;
