@@ -131,7 +131,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.002)                    # the timed region of a small config lasts ~10 ms
 
     def start(self):
         if self.nv:
