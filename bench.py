@@ -67,6 +67,9 @@ def parse_args():
     ap.add_argument("--gather", choices=["peer", "nccl"], default="peer",
                     help="--shard rows: peer = interleaved bands stored straight into rank 0's frame over NVLink (CUDA IPC); "
                          "nccl = contiguous tiles gathered point to point")
+    ap.add_argument("--reduce", choices=["peer", "nccl"], default="peer",
+                    help="--shard samples: peer = deterministic pull-reduce kernel over the CUDA-IPC-mapped partial frames; nccl = dist.reduce")
+    ap.add_argument("--no-subrecords", action="store_true", help="N > 1: skip the c4_samples / c5_rows sub-records")
     ap.add_argument("--flags", type=lambda s: int(s, 0), default=0, help="extra RT_FLAG_* bits (e.g. 0x2 parity math)")
     ap.add_argument("--host-path", type=int, default=0, help="rt_set_host_path: 0 auto, 1 staged, 2 banded, 3 zero-copy")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -100,8 +103,9 @@ def workload_for(args):
 class ClockSampler:
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, period_s: float = 0.002):
         self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self.period_s, self.power = period_s, []
         self._stop = threading.Event()
         self._t = None
         try:
@@ -125,13 +129,14 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for k, bit in names.items():
                     if r & bit:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.002)                    # the timed region of a small config lasts ~10 ms
+            self._stop.wait(self.period_s)            # the timed region of a small config lasts ~10 ms
 
     def start(self):
         if self.nv:
@@ -144,7 +149,28 @@ class ClockSampler:
             self._t.join()
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "sm_mhz_min": s[0] if s else None, "power_w_max": max(self.power) if self.power else None}
+
+
+def host_threads() -> int:
+    """The CPUs this process may run on. torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU
+    arm passes this count to the oracle explicitly (an OpenMP num_threads clause), so that setting is ignored."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def config_for(w, args, world: int, parallelism: str, **extra) -> dict:
+    """The ``config`` object — the SAME key set for both arms of the bench."""
+    cfg = {"workload": f"{w.name}: {w.description}", "width": w.width, "height": w.height, "objects": len(w.objects),
+           "lights": len(w.lights), "max_ray_depth": w.max_ray_depth, "num_samples": max(1, w.num_samples),
+           "parallelism": parallelism, "l2": None, "rays_per_frame": None, "rays_per_pixel": None, "math": None,
+           "rays": "reference-literal: 1 ray = 1 intersectObjects call of the shader on this input (the kernels prove most "
+                   "of them unnecessary and skip them)",
+           "variant": None, "note": None}
+    cfg.update(extra)
+    return cfg
 
 
 def cpu_baseline(w, kind: str, budget_s: float = 15.0, step: int = 0) -> dict:
@@ -155,11 +181,11 @@ def cpu_baseline(w, kind: str, budget_s: float = 15.0, step: int = 0) -> dict:
         kind = "port"
     if kind == "port":
         oracle.build_port()
-    cores = os.cpu_count() or 1
+    cores = host_threads()
     # calibrate on a sparse subset, then size the timed sample to ~budget_s of CPU work
-    oracle.render(w, kind, x0=0, y0=0, sx=1, sy=1, nx=4, ny=4)      # warm: library load, skybox conversion
+    oracle.render(w, kind, x0=0, y0=0, sx=1, sy=1, nx=4, ny=4, threads=cores)      # warm: library load, skybox conversion
     t0 = time.perf_counter()
-    cal = oracle.render(w, "port", x0=3, y0=5, sx=32, sy=32)
+    cal = oracle.render(w, "port", x0=3, y0=5, sx=32, sy=32, threads=cores)
     t_cal = time.perf_counter() - t0
     px_cal = cal["color"].shape[0] * cal["color"].shape[1] * max(1, w.num_samples)
     per_px = t_cal / max(px_cal, 1)
@@ -172,13 +198,13 @@ def cpu_baseline(w, kind: str, budget_s: float = 15.0, step: int = 0) -> dict:
     best, rays = None, 0
     for _ in range(2):
         t0 = time.perf_counter()
-        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step)
+        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step, threads=cores)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
-    rays = oracle.render(w, "port", x0=x0, y0=y0, sx=step, sy=step)["counters"]["rays"]
+    rays = oracle.render(w, "port", x0=x0, y0=y0, sx=step, sy=step, threads=cores)["counters"]["rays"]
     return {"value": rays / best / 1e6, "unit": METRIC, "cores": cores, "kind": kind,
             "sample": f"{w.name} {w.width}x{w.height}, every {step}-th pixel in x and y (offset {x0},{y0}), "
-                      f"{rays} rays in {best:.3f} s, best of 2, OpenMP dynamic over rows",
+                      f"{rays} rays in {best:.3f} s, best of 2, OpenMP dynamic over rows on {cores} threads",
             "seconds": best, "rays": rays, "step": step}
 
 
@@ -193,32 +219,63 @@ def run_reference(args) -> None:
     kind = "reference" if oracle.have("reference") else "port"
     base = cpu_baseline(w, kind, budget_s=6.0, step=args.cpu_sample_step)
     step, x0, y0 = base["step"], 3 % base["step"], 5 % base["step"]
+    cores = base["cores"]
     for _ in range(max(0, args.warmup - 1)):
-        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step)
+        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step, threads=cores)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step)
+        oracle.render(w, kind, x0=x0, y0=y0, sx=step, sy=step, threads=cores)
     dt = (time.perf_counter() - t0) / max(1, args.steps)
     val = base["rays"] / dt / 1e6
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{w.name}: {w.description}", "width": w.width, "height": w.height,
-                   "max_ray_depth": w.max_ray_depth, "num_samples": w.num_samples,
-                   "note": "reference shader source compiled as C++ on host cores; GL/llvmpipe unavailable on this box"},
-        "cpu_baseline": {"value": val, "unit": METRIC, "cores": base["cores"], "kind": base["kind"], "sample": base["sample"]},
+        "config": config_for(w, args, 1, f"{cores} host threads (OpenMP), no GPU", math="IEEE FP32, -ffp-contract=off",
+                             note="reference shader source compiled as C++ on host cores; GL/llvmpipe unavailable on this box; "
+                                  "each step = " + base["sample"]),
+        "cpu_baseline": {"value": val, "unit": METRIC, "cores": cores, "kind": base["kind"], "sample": base["sample"]},
         "e2e": {"value": val, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
 
 
+def executed_work(name: str, W: int, H: int) -> dict | None:
+    """FP32 thread-instructions one launch of this config EXECUTES, from the committed ncu capture of this build
+    (profiles/executed.json, written by tools/ncu_executed.py from a `ncu --set full` report): the algorithmic
+    flop count is the reference-literal algorithm's, which the kernels mostly prove unnecessary at C3-C5."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "executed.json"))).get(f"{name}@{W}x{H}")
+    except Exception:
+        return None
+
+
+def sustained_leg(ctx, params, out, stream, dev, kern_ms: float, local: int, seconds: float = 2.0) -> dict:
+    """>= `seconds` of back-to-back frames (no L2 flush, no host sync in between) with NVML sampled throughout:
+    shows whether the clock of the short timed region holds under load."""
+    import torch
+    n = max(10, int(seconds * 1e3 / max(kern_ms, 1e-3)) + 1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local, period_s=0.01)
+    torch.cuda.synchronize(dev)
+    sampler.start()
+    e0.record(stream)
+    for _ in range(n):
+        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    c = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    return {"frames": n, "seconds": ms * 1e-3, "ms_per_frame": ms / n, "sm_mhz_median": c["sm_mhz"], "sm_mhz_min": c.get("sm_mhz_min"),
+            "power_w_max": c.get("power_w_max"), "reasons": c["reasons"], "samples": c["samples"]}
+
+
 def run_ours(args) -> None:
     import numpy as np
     import torch
     import torch.distributed as dist
-    from opengl_raytracing_b200 import abi, sharding
+    from opengl_raytracing_b200 import abi, sharding, synthetic
     from opengl_raytracing_b200.pipeline import RtContext, bind_workload, workload_params
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -261,7 +318,8 @@ def run_ours(args) -> None:
         scaling, par = "strong", f"row tiles x{world}, gathered to rank 0"
     elif world > 1:
         params = workload_params(w, flags=flags | abi.FLAG_SUM_SAMPLES, frame_count=w.frame_count + rank * ns)
-        scaling, par = "weak", f"sample ranges x{world} ({ns} spp per rank), NCCL reduce to rank 0"
+        scaling, par = "weak", (f"sample ranges x{world} ({ns} spp per rank), partial sums reduced to rank 0 "
+                                f"({'peer pull-reduce kernel over CUDA IPC' if args.reduce == 'peer' else 'NCCL reduce'})")
     else:
         params = workload_params(w, flags=flags)
         scaling, par = "weak", "single GPU"
@@ -271,6 +329,10 @@ def run_ours(args) -> None:
     normal = torch.zeros(H, W, 4, dtype=torch.float16, device=dev)
     write_geom = (world == 1) or args.shard == "rows" or rank == 0
     stream = torch.cuda.current_stream(dev)
+    reducer = None
+    if world > 1 and args.shard == "samples" and args.reduce == "peer":
+        reducer = sharding.PeerReducer(ctx, H, W)      # partial frames of every rank mapped into every rank (CUDA IPC)
+        color = reducer.partial                         # this rank renders its partial sum into its exported buffer
 
     # ---- reference-literal op counts for THIS rank's work (untimed, counter variant)
     pc = abi.FrameParams.from_buffer_copy(params)
@@ -285,21 +347,28 @@ def run_ours(args) -> None:
 
     out = (peer.color, peer.position, peer.normal) if peer else (color, position if write_geom else None, normal if write_geom else None)
 
-    def step():
-        if params.flags & abi.FLAG_ACCUMULATE:
-            color.zero_()
-        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
+    def collective():
         if peer:
             dist.barrier()                             # the frame is complete on rank 0 when every rank's kernel is
         elif world > 1 and args.shard == "rows":
             for buf in (color, position, normal):
                 sharding.gather_rows(buf, H, world)
+        elif reducer:
+            reducer.reduce(stream.cuda_stream, ns * world)
         elif world > 1:
             sharding.reduce_samples(color, ns * world)
 
-    # untimed warm-up: at least 6 frames, so that the library's per-scene variant choice for large
-    # scenes (1 untimed + 4 timed trial frames, rt_abi.cu) has settled before the timed region
-    nwarm = max(6, args.warmup)
+    def step():
+        if params.flags & abi.FLAG_ACCUMULATE:
+            color.zero_()
+        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
+        collective()
+
+    # ---- the variant is chosen ONCE, explicitly (rt_tune: every applicable variant timed on this scene and
+    # frame shape, identical images), so that no warm-up or timed frame is a trial frame of the autotuner
+    ctx.set_autotune(False)
+    tuning = ctx.tune(params)
+    nwarm = max(3, args.warmup)
     for _ in range(nwarm):
         step()
     torch.cuda.synchronize(dev)
@@ -321,13 +390,7 @@ def run_ours(args) -> None:
             color.zero_()
         ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
         ev[i][1].record(stream)
-        if peer:
-            dist.barrier()
-        elif world > 1 and args.shard == "rows":
-            for buf in (color, position, normal):
-                sharding.gather_rows(buf, H, world)
-        elif world > 1:
-            sharding.reduce_samples(color, ns * world)
+        collective()
         ev[i][2].record(stream)
     torch.cuda.synchronize(dev)
     if world > 1:
@@ -347,25 +410,53 @@ def run_ours(args) -> None:
         rays_total, flops_total = float(rays_rank), float(flops_rank)
     value = rays_total / (step_ms * 1e-3) / 1e6
 
-    # ---- e2e through the C ABI with host buffers (rank-local frame; aggregate over ranks)
+    sustained = sustained_leg(ctx, params, out, stream, dev, kern_ms, local) if rank == 0 or world > 1 else None
+    if world > 1:
+        dist.barrier()
+
+    # ---- e2e: the SAME job through host buffers. Every step: scene H2D on every rank (ssbo.update()), this rank's
+    # render, the exchange step of the sharding, and the finished frame's three images landing in pinned host
+    # memory on rank 0. N = 1: the single C-ABI call rt_render_host does all of it.
     if params.row_band > 0:
         nb = (H + params.row_band - 1) // params.row_band
         px = sum(min(params.row_band, H - k * params.row_band) for k in range(params.row_phase, nb, params.row_period)) * W
     else:
         px = (params.row_end - params.row_begin) * W
-    h = {}
-    for name, nbytes in (("color", px * 16), ("position", px * 16), ("normal", px * 8)):
-        p = abi.C.c_void_p(0)
-        assert ctx.lib.rt_host_alloc(abi.C.byref(p), H * W * (16 if name != "normal" else 8)) == 0
-        h[name] = p
     objs = np.ascontiguousarray(w.objects); lights = np.ascontiguousarray(w.lights)
-    pe = abi.FrameParams.from_buffer_copy(params)
-    pe.flags = params.flags & ~(abi.FLAG_ACCUMULATE | abi.FLAG_SUM_SAMPLES)
-    assert ctx.lib.rt_set_host_path(ctx.handle, args.host_path) == 0
-    def e2e_step():
-        st = ctx.lib.rt_render_host(ctx.handle, abi.C.byref(pe), objs.ctypes.data, len(objs), lights.ctypes.data, len(lights),
-                                    h["color"], h["position"], h["normal"], None)
-        assert st == 0, ctx.lib.rt_last_error(ctx.handle)
+    h2d = objs.nbytes + lights.nbytes
+    if world == 1:
+        h = {}
+        for name in ("color", "position", "normal"):
+            p = abi.C.c_void_p(0)
+            assert ctx.lib.rt_host_alloc(abi.C.byref(p), H * W * (16 if name != "normal" else 8)) == 0
+            h[name] = p
+        pe = abi.FrameParams.from_buffer_copy(params)
+        assert ctx.lib.rt_set_host_path(ctx.handle, args.host_path) == 0
+
+        def e2e_step():
+            st = ctx.lib.rt_render_host(ctx.handle, abi.C.byref(pe), objs.ctypes.data, len(objs), lights.ctypes.data, len(lights),
+                                        h["color"], h["position"], h["normal"], None)
+            assert st == 0, ctx.lib.rt_last_error(ctx.handle)
+        e2e_call = "rt_render_host: scene H2D (pinned staging) + rt_render + D2H of colour/position/normal into pinned host buffers"
+        d2h = px * 40
+    else:
+        hbuf = None
+        if rank == 0:
+            hbuf = (torch.empty(H, W, 4, dtype=torch.float32).pin_memory(), torch.empty(H, W, 4, dtype=torch.float32).pin_memory(),
+                    torch.empty(H, W, 4, dtype=torch.float16).pin_memory())
+        frame = peer.tensors() if (peer and rank == 0) else (color, position, normal)
+
+        def e2e_step():
+            ctx.upload_scene(objs, lights, stream.cuda_stream, async_=True)
+            step()
+            if rank == 0:
+                final = (reducer.result if reducer else frame[0], frame[1], frame[2])
+                for dst, src in zip(hbuf, final):
+                    dst.copy_(src, non_blocking=True)
+            torch.cuda.synchronize(dev)
+        e2e_call = ("every rank: rt_upload_scene (H2D) + rt_render of its shard; the sharding's exchange step; rank 0: D2H of the "
+                    "finished colour/position/normal into pinned host memory")
+        d2h = H * W * 40
     for _ in range(3):
         e2e_step()
     if world > 1:
@@ -374,15 +465,18 @@ def run_ours(args) -> None:
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         e2e_step()
+    if world > 1:
+        dist.barrier()
     e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
     te = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_ms = float(te[0])
-    for p in h.values():
-        ctx.lib.rt_host_free(p)
-    h2d = objs.nbytes + lights.nbytes
-    d2h = px * 40
+    if world == 1:
+        for p in h.values():
+            ctx.lib.rt_host_free(p)
+
+    sub = multi_gpu_subrecords(args, rank, world, local) if (world > 1 and not args.no_subrecords) else None
 
     if rank == 0:
         peaks = {}
@@ -396,37 +490,52 @@ def run_ours(args) -> None:
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{w.name}@{W}x{H}", {}).get("bytes")
         except Exception:
             pass
+        roof = {"bound": "fp32", "achieved": ach_tf, "peak": fp32_peak["tflops"], "unit": "TFLOP/s",
+                "frac": ach_tf / fp32_peak["tflops"], "traffic": traffic,
+                "traffic_source": "profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed "
+                                  "ncu --set full capture of this config (a constant of the build, not measured in this run)",
+                "peak_source": "measured in this run: FFMA-only micro-kernel (rt_measure_fp32_peak); "
+                               "MEASURED_PEAKS.json has no FP32 entry",
+                "algorithmic_flops_per_launch": flops_rank, "algorithmic_sfu_ops_per_launch": sfu_rank,
+                "flop_model": "v0 (SURVEY.md 8d), reference-literal op counts x fixed constants",
+                "hbm_write": {"bytes_per_launch": px * 40, "achieved_gbs": px * 40 / (kern_ms * 1e-3) / 1e9,
+                              "peak_gbs": peaks.get("hbm_gbs"), "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)"}}
+        ex = executed_work(w.name, W, H)
+        if ex:
+            fl = ex["fadd"] + ex["fmul"] + 2 * ex["ffma"]
+            etf = fl / (kern_ms * 1e-3) / 1e12
+            roof["executed"] = {"fp32_flops_per_launch": fl, "achieved": etf, "frac": etf / fp32_peak["tflops"], "unit": "TFLOP/s",
+                                "fp32_lane_utilisation": (ex["fadd"] + ex["fmul"] + ex["ffma"]) / (kern_ms * 1e-3) / (fp32_peak["tflops"] * 1e12 / 2),
+                                "source": ex.get("source"), "kernels": ex.get("kernels"),
+                                "note": "FADD + FMUL + 2 FFMA thread-instructions of the committed ncu capture of this config and build / this run's time"}
         line = {
-            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": nwarm,
-            "ms_per_step": step_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "warmup_effective": nwarm, "ms_per_step": step_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{w.name}: {w.description}", "width": W, "height": H, "objects": len(w.objects),
-                       "lights": len(w.lights), "max_ray_depth": w.max_ray_depth, "num_samples": ns,
-                       "parallelism": par, "l2": "flushed between timed iterations (256 MB fill, untimed)",
-                       "rays_per_frame": rays_rank, "rays_per_pixel": rays_rank / (px * 1.0),
-                       "math": "parity" if (flags & abi.FLAG_PARITY_MATH) else "fast"},
+            "config": config_for(w, args, world, par, l2="flushed between timed iterations (256 MB fill, untimed)",
+                                 rays_per_frame=rays_rank, rays_per_pixel=rays_rank / (px * 1.0),
+                                 math="parity" if (flags & abi.FLAG_PARITY_MATH) else "fast", variant=tuning),
             "ms_per_frame": kern_ms,
-            "roofline": {"bound": "fp32", "achieved": ach_tf, "peak": fp32_peak["tflops"], "unit": "TFLOP/s",
-                         "frac": ach_tf / fp32_peak["tflops"], "traffic": traffic,
-                         "peak_source": "measured in this run: FFMA-only micro-kernel (rt_measure_fp32_peak); "
-                                        "MEASURED_PEAKS.json has no FP32 entry",
-                         "algorithmic_flops_per_launch": flops_rank, "algorithmic_sfu_ops_per_launch": sfu_rank,
-                         "flop_model": "v0 (SURVEY.md 8d), reference-literal op counts x fixed constants",
-                         "hbm_write": {"bytes_per_launch": px * 40, "achieved_gbs": px * 40 / (kern_ms * 1e-3) / 1e9,
-                                       "peak_gbs": peaks.get("hbm_gbs"), "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)"}},
+            "roofline": roof,
             "e2e": {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": METRIC, "ms_per_step": e2e_ms,
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "call": "rt_render_host: scene H2D (pinned staging) + rt_render + D2H of colour/position/normal into pinned host buffers"},
+                    "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h, "call": e2e_call},
             "gpu_launches": launches,
             "clocks": clocks,
+            "sustained": sustained,
             "wall_s_timed_region": t_wall,
         }
+        if sub:
+            line.update(sub)
         if not args.no_cpu_baseline and world == 1:
             import oracle
             kind = "reference" if oracle.have("reference") else "port"
             cb = cpu_baseline(w, kind, budget_s=12.0, step=args.cpu_sample_step)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         emit(line)
+    if reducer:
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        reducer.close()
     if peer:
         torch.cuda.synchronize(dev)
         dist.barrier()
@@ -434,6 +543,110 @@ def run_ours(args) -> None:
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def multi_gpu_subrecords(args, rank: int, world: int, local: int) -> dict:
+    """The two configs north_star names for sharding, run in the same processes after the headline job:
+      c4_samples  3840x2160, 64 spp split into `world` sample ranges + the reduce to rank 0 (strong scaling)
+      c5_rows     7680x4320, interleaved 32-row bands, kernel stores straight into rank 0's frame over NVLink
+    each with the same job on ONE GPU of the same box (every rank runs it on its own GPU at the same time; rank 0's
+    time is reported) for the speed-up."""
+    import torch
+    import torch.distributed as dist
+    from opengl_raytracing_b200 import abi, sharding, synthetic
+    from opengl_raytracing_b200.pipeline import RtContext, bind_workload, workload_params
+    dev = torch.device("cuda", local)
+    stream = torch.cuda.current_stream(dev)
+    out = {}
+
+    def timed(fn, steps, warm=1):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize(dev); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+        t0 = t.clone()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t0[0])
+
+    def pin_variant(ctx, w, **over):
+        """Choose the variant on a 1-sample frame of the same shape (seconds, not minutes) and pin it."""
+        ctx.set_autotune(False)
+        t = ctx.tune(workload_params(w, num_samples=1, **over))
+        ctx.set_tuning({"megakernel": abi.KERNEL_MEGAKERNEL, "wavefront": abi.KERNEL_WAVEFRONT}[t["kernel"]],
+                       1 if t["registers"] == 80 else 0, t["phase_level"])
+        return t
+
+    # ---- C4: sample ranges
+    w = synthetic.config(4)
+    H, W, S = w.height, w.width, w.num_samples
+    ctx = RtContext(local)
+    bind_workload(ctx, w)
+    var = pin_variant(ctx, w)
+    first, count = sharding.sample_range(S, rank, world)
+    use_peer = args.reduce == "peer"
+    reducer = sharding.PeerReducer(ctx, H, W) if use_peer else None
+    part = reducer.partial if reducer else torch.zeros(H, W, 4, device=dev)
+    pos = torch.zeros(H, W, 4, device=dev) if rank == 0 else None
+    nrm = torch.zeros(H, W, 4, dtype=torch.float16, device=dev) if rank == 0 else None
+    p = workload_params(w, flags=abi.FLAG_SUM_SAMPLES, frame_count=w.frame_count + first, num_samples=max(count, 1))
+
+    def c4_step():
+        if count > 0:
+            ctx.render(p, part, pos, nrm, None, stream.cuda_stream)
+        else:
+            part.zero_()
+        if reducer:
+            reducer.reduce(stream.cuda_stream, S)
+        else:
+            sharding.reduce_samples(part, S)
+    ms_n, _ = timed(c4_step, steps=2)
+    full = torch.zeros(H, W, 4, device=dev)
+    p1 = workload_params(w)
+    _, ms_1 = timed(lambda: ctx.render(p1, full, None, None, None, stream.cuda_stream), steps=1)
+    out["c4_samples"] = {"workload": f"{w.name}: {w.description}", "ms_per_step": ms_n, "ms_per_step_1gpu_same_box": ms_1,
+                         "speedup": ms_1 / ms_n, "efficiency": ms_1 / ms_n / world, "samples_per_rank": count,
+                         "exchange": ("peer pull-reduce kernel (rank r sums slice r of all partials in rank order, RGB, into rank 0's frame)"
+                                      if use_peer else "NCCL reduce of the RGBA32F partial sums to rank 0"),
+                         "nvlink_bytes_into_rank0": (world - 1) * H * W * 16 // world if use_peer else None,
+                         "variant": var}
+    if reducer:
+        torch.cuda.synchronize(dev); dist.barrier(); reducer.close()
+    del part, full
+    ctx.close()
+
+    # ---- C5: interleaved row bands, fused peer stores
+    w = synthetic.config(5)
+    H, W = w.height, w.width
+    ctx = RtContext(local)
+    bind_workload(ctx, w)
+    bp = sharding.band_plan(rank, world)
+    var = pin_variant(ctx, w, **bp)
+    peer = sharding.PeerFrame(ctx, H, W)
+    p = workload_params(w, **bp)
+
+    def c5_step():
+        ctx.render(p, peer.color, peer.position, peer.normal, None, stream.cuda_stream)
+        dist.barrier()
+    ms_n, _ = timed(c5_step, steps=5, warm=2)
+    c = torch.zeros(H, W, 4, device=dev); po = torch.zeros(H, W, 4, device=dev); no = torch.zeros(H, W, 4, dtype=torch.float16, device=dev)
+    ctx.set_tuning(None)
+    var1 = pin_variant(ctx, w)
+    p1 = workload_params(w)
+    _, ms_1 = timed(lambda: ctx.render(p1, c, po, no, None, stream.cuda_stream), steps=3, warm=1)
+    out["c5_rows"] = {"workload": f"{w.name}: {w.description}", "ms_per_step": ms_n, "ms_per_step_1gpu_same_box": ms_1,
+                      "speedup": ms_1 / ms_n, "efficiency": ms_1 / ms_n / world,
+                      "exchange": f"none: interleaved {sharding.BAND_ROWS}-row bands, float4 stores over NVLink into rank 0's frame, one barrier",
+                      "nvlink_bytes_into_rank0": (world - 1) * H * W * 40 // world, "variant": var, "variant_1gpu": var1}
+    torch.cuda.synchronize(dev); dist.barrier()
+    peer.close()
+    ctx.close()
+    return out
 
 
 _REAL_STDOUT = None

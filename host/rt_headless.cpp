@@ -6,6 +6,8 @@
 //   rt_headless --resave in.scene out.scene          (Load + Save round trip; needs no GPU)
 //   rt_headless --resave-v2 in.scene out.scene       (Load + SaveV2: the lossless OBJECT2 / LIGHT2 records)
 //
+//   rt_headless --scene default.scene --gpus 0,1,2,3 --shard rows|samples ...   (several GPUs: include/rt_multi.h)
+//
 //   rt_headless --scene default.scene --post --frames 8 --out /tmp/frame   (whole iterations: ray tracing +
 //                                        bloom + TAA on device-resident images; writes <out>_display.ppm)
 //
@@ -14,6 +16,8 @@
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
+#include <memory>
+#include <sstream>
 
 #include "rt_host.hpp"
 
@@ -23,7 +27,7 @@ static int usage() {
   std::fprintf(stderr,
                "usage: rt_headless --scene FILE [--size W H] [--frames N] [--depth D] [--samples S] [--flags F]\n"
                "                   [--camera px py pz yaw pitch fov] [--noise FILE W H] [--skybox FILE SIZE CH f16|f32]\n"
-               "                   [--device N] [--out PREFIX] [--raw] [--post]\n"
+               "                   [--device N | --gpus A,B,... [--shard rows|samples]] [--out PREFIX] [--raw] [--post]\n"
                "       rt_headless --dump-scene IN.scene OUT.bin\n"
                "       rt_headless --resave IN.scene OUT.scene\n"
                "       rt_headless --resave-v2 IN.scene OUT.scene\n");
@@ -70,6 +74,8 @@ int main(int argc, char** argv) {
   int W = 800, H = 800, frames = 1, depth = 3, samples = 1, device = 0;   // src/global.cpp:4-5: 800 x 800
   int noise_w = 0, noise_h = 0, sky_size = 0, sky_ch = 4;
   bool sky_f16 = true, raw = false, have_cam = false, post = false;
+  std::vector<int> gpus;
+  int sharding = RT_MULTI_ROWS;
   unsigned flags = 0;
   float cam[6] = {0, 0, 0, -90, 0, 45};
   for (int i = 1; i < argc; ++i) {
@@ -82,6 +88,8 @@ int main(int argc, char** argv) {
     else if (a == "--samples") { need(1); samples = std::atoi(argv[++i]); }
     else if (a == "--flags") { need(1); flags = (unsigned)std::strtoul(argv[++i], nullptr, 0); }
     else if (a == "--device") { need(1); device = std::atoi(argv[++i]); }
+    else if (a == "--gpus") { need(1); std::stringstream ss(argv[++i]); std::string tok; while (std::getline(ss, tok, ',')) gpus.push_back(std::atoi(tok.c_str())); }
+    else if (a == "--shard") { need(1); sharding = std::string(argv[++i]) == "samples" ? RT_MULTI_SAMPLES : RT_MULTI_ROWS; }
     else if (a == "--out") { need(1); out = argv[++i]; }
     else if (a == "--raw") raw = true;
     else if (a == "--post") post = true;
@@ -93,7 +101,9 @@ int main(int argc, char** argv) {
   if (scene.empty()) return usage();
 
   try {
-    ForwardShadingPipeline pipeline(W, H, device);
+    std::unique_ptr<ForwardShadingPipeline> owned(gpus.empty() ? new ForwardShadingPipeline(W, H, device)
+                                                               : new ForwardShadingPipeline(W, H, gpus, sharding));
+    ForwardShadingPipeline& pipeline = *owned;
     if (!pipeline.LoadScene(scene)) { std::fprintf(stderr, "cannot open %s\n", scene.c_str()); return 1; }
     if (!noise_file.empty()) {
       const std::vector<unsigned char> n = ReadRaw(noise_file);
@@ -122,7 +132,7 @@ int main(int argc, char** argv) {
     std::printf("{\"scene\": \"%s\", \"objects\": %zu, \"lights\": %zu, \"width\": %d, \"height\": %d, \"frames\": %d, "
                 "\"ms_per_frame_host\": %.4f, \"launches\": %llu}\n",
                 scene.c_str(), pipeline.ssbo.objects.size(), pipeline.lightSSBO.lights.size(), W, H, frames, ms / frames,
-                (unsigned long long)rt_launch_count(pipeline.context()));
+                (unsigned long long)pipeline.launches());
     const size_t px = (size_t)W * H;
     if (post) {                                                  // what the window would show
       if (!WritePPM(out + "_display.ppm", pipeline.displayTex.data(), W, H)) throw std::runtime_error("cannot write " + out + "_display.ppm");

@@ -30,6 +30,7 @@
 
 #include "rt_abi.h"
 #include "rt_frame.h"
+#include "rt_multi.h"
 
 namespace rtb200 {
 
@@ -400,11 +401,21 @@ class ForwardShadingPipeline {
     check(nullptr, rt_create(&ctx_, device), "rt_create");
     Init();
   }
+  // Several GPUs of the box behind the same Render(): include/rt_multi.h (devices[0] holds the images;
+  // sharding = RT_MULTI_ROWS or RT_MULTI_SAMPLES). RenderFrame (the post chain) stays on one GPU.
+  ForwardShadingPipeline(int width, int height, const std::vector<int>& devices, int sharding) : WIDTH(width), HEIGHT(height), sharding_(sharding) {
+    if (rt_abi_version() != RT_ABI_VERSION) throw std::runtime_error("librt_b200.so: ABI version mismatch");
+    const rt_status st = rt_multi_create(&multi_, devices.data(), (int)devices.size());
+    if (st != RT_OK) throw std::runtime_error(std::string("rt_multi_create: ") + rt_status_string(st));
+    ctx_ = rt_multi_context(multi_, 0);
+    Init();
+  }
   ForwardShadingPipeline(const ForwardShadingPipeline&) = delete;
   ForwardShadingPipeline& operator=(const ForwardShadingPipeline&) = delete;
   ~ForwardShadingPipeline() {
     if (frame_) rt_frame_destroy(frame_);  // a frame goes before its context
-    if (ctx_) rt_destroy(ctx_);
+    if (multi_) rt_multi_destroy(multi_);  // owns its contexts
+    else if (ctx_) rt_destroy(ctx_);
   }
 
   void Init() {
@@ -414,10 +425,14 @@ class ForwardShadingPipeline {
     gNormalTex.reset(px * 4);             // 4 x fp16 per pixel
   }
   // InitBlueNoiseTex (:39-49): R8, REPEAT wrap. The reference decodes a PNG; here raw bytes.
-  void SetNoise(const unsigned char* r8, int w, int h) { check(ctx_, rt_set_noise(ctx_, r8, w, h), "rt_set_noise"); }
+  void SetNoise(const unsigned char* r8, int w, int h) {
+    if (multi_) mcheck(rt_multi_set_noise(multi_, r8, w, h), "rt_multi_set_noise");
+    else check(ctx_, rt_set_noise(ctx_, r8, w, h), "rt_set_noise");
+  }
   // glBindTexture(GL_TEXTURE_CUBE_MAP, ...) (:167-170): 6 faces (+X,-X,+Y,-Y,+Z,-Z) of size^2 texels.
   void SetSkybox(const void* faces, int face_size, int channels, bool fp16) {
-    check(ctx_, rt_set_skybox(ctx_, faces, face_size, channels, fp16 ? 1 : 0), "rt_set_skybox");
+    if (multi_) mcheck(rt_multi_set_skybox(multi_, faces, face_size, channels, fp16 ? 1 : 0), "rt_multi_set_skybox");
+    else check(ctx_, rt_set_skybox(ctx_, faces, face_size, channels, fp16 ? 1 : 0), "rt_set_skybox");
     skyboxEnabled = faces != nullptr;
   }
   bool LoadScene(const std::string& path) {
@@ -448,6 +463,14 @@ class ForwardShadingPipeline {
     const bool upload = ssbo.dirty || lightSSBO.dirty;
     SetUniforms();
     rt_frame_params& p = raytracingShader.params;
+    if (multi_) {
+      mcheck(rt_multi_render_host(multi_, &p, sharding_, upload ? ssbo.objects.data() : nullptr, (int)ssbo.objects.size(),
+                                  upload ? lightSSBO.lights.data() : nullptr, (int)lightSSBO.lights.size(),
+                                  outputTex.data(), gPositionTex.data(), gNormalTex.data(), nullptr), "rt_multi_render_host");
+      ssbo.dirty = lightSSBO.dirty = false;
+      if (taaEnabled) ++frameCount;
+      return;
+    }
     if (upload)                            // ssbo.update() + lightSSBO.update() (src/SSBO.h:16-23)
       check(ctx_, rt_upload_scene(ctx_, ssbo.objects.data(), (int)ssbo.objects.size(), lightSSBO.lights.data(),
                                   (int)lightSSBO.lights.size(), nullptr, 0), "rt_upload_scene");
@@ -474,6 +497,7 @@ class ForwardShadingPipeline {
   // the reference's GL textures do. The presented image lands in displayTex (8-bit UNORM, the
   // window's framebuffer) — and, on request, in displayTexF (RGBA32F, before that conversion).
   void RenderFrame(bool readFloat = false) {
+    if (multi_) throw std::runtime_error("RenderFrame: the post chain reads the whole image; a frame is not sharded (use one GPU)");
     if (!frame_) {
       check(ctx_, rt_frame_create(ctx_, WIDTH, HEIGHT, &frame_), "rt_frame_create");
       displayTex.reset((size_t)WIDTH * HEIGHT * 4);
@@ -501,6 +525,8 @@ class ForwardShadingPipeline {
 
   rt_context* context() { return ctx_; }
   rt_frame* frame() { return frame_; }
+  rt_multi* multi() { return multi_; }
+  uint64_t launches() { return multi_ ? rt_multi_launch_count(multi_) : rt_launch_count(ctx_); }
 
   const int WIDTH, HEIGHT;                 // src/global.cpp:4-5
   Camera camera;
@@ -521,8 +547,13 @@ class ForwardShadingPipeline {
   bool taaEnabled = true;
 
  private:
+  void mcheck(rt_status st, const char* what) {
+    if (st != RT_OK) throw std::runtime_error(std::string(what) + ": " + rt_multi_last_error(multi_));
+  }
   rt_context* ctx_ = nullptr;
   rt_frame* frame_ = nullptr;
+  rt_multi* multi_ = nullptr;
+  int sharding_ = RT_MULTI_ROWS;
 };
 
 // ---------------------------------------------------------------- image writers (headless "display")

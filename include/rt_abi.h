@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 2
+#define RT_ABI_VERSION 3
 
 /* ------------------------------------------------------------------------- */
 /* Data contracts: byte-exact std430 layouts (== the alignas() C++ structs).   */
@@ -219,7 +219,9 @@ rt_status rt_set_noise(rt_context* ctx, const unsigned char* r8, int w, int h);
  * RT_FLAG_NORMAL_FP32. d_object_id: optional int32 per pixel (last-hit object index,
  * -1 on a primary miss), may be NULL. Any of the three image pointers may be NULL to
  * skip that store. The pointers may be peer-mapped (NVLink) addresses.
- * Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the legacy default stream). */
+ * Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the legacy default stream). Launches of
+ * one context may overlap on different streams (each takes its own work counter); the CALLS
+ * themselves must come from one thread at a time.                                            */
 rt_status rt_render(rt_context* ctx, const rt_frame_params* params,
                     float* d_color_rgba32f, float* d_position_rgba32f,
                     void* d_normal, int32_t* d_object_id, void* cuda_stream);
@@ -272,6 +274,45 @@ rt_status rt_measure_fp32_peak(rt_context* ctx, double* tflops, int* sm_count, d
 
 /* Device kernel launch counter (every kernel this library launched on ctx). */
 uint64_t  rt_launch_count(rt_context* ctx);
+
+/* ------------------------------------------------------------------------- */
+/* Kernel variants and their tuning.                                           */
+/* The pass exists in several builds that produce IDENTICAL images (same per-pixel arithmetic,
+ * different scheduling): the persistent megakernel (rt_packet.cuh) at two register budgets, with
+ * independent warps or CTA-coherent phases, and the wavefront pipeline (rt_wavefront.cuh:
+ * trace / shadow-job / shade kernels over compacted ray queues). Which is fastest depends on the
+ * scene. The reference has no counterpart (one GLSL program, src/ForwardShadingPipeline.cpp:153);
+ * a caller that edits the scene every frame (src/ImGUIManager.cpp:197-202) uses rt_tune once per
+ * scene shape, or rt_set_tuning to pin a variant, and never renders a trial frame.            */
+/* ------------------------------------------------------------------------- */
+enum { RT_KERNEL_AUTO = -1, RT_KERNEL_MEGAKERNEL = 0, RT_KERNEL_WAVEFRONT = 1, RT_KERNEL_LITERAL = 2 };
+enum { RT_TUNING_DEFAULT = 0,    /* nothing measured for this shape: the built-in default variant  */
+       RT_TUNING_TRIALS  = 1,    /* autotune is timing variants on the caller's launches            */
+       RT_TUNING_CHOSEN  = 2,    /* measured (rt_tune or autotune); the fastest variant is in use   */
+       RT_TUNING_PINNED  = 3 };  /* rt_set_tuning                                                   */
+typedef struct rt_tuning {
+  int32_t kernel;          /* RT_KERNEL_*                                                            */
+  int32_t registers;       /* megakernel, large scenes: 0 = 128 registers (2 CTAs/SM), 1 = 80 (3)    */
+  int32_t phase_level;     /* megakernel: 0 independent warps, 1..3 CTA-coherent phases              */
+  int32_t state;           /* RT_TUNING_* (output only)                                              */
+  int32_t num_variants;    /* how many variants apply to this scene / launch shape (output only)     */
+  float   variant_ms[8];   /* best measured time of each, 0 = not measured (output only)            */
+  int32_t variant_kernel[8], variant_registers[8], variant_phase_level[8];
+} rt_tuning;
+
+/* Times every applicable variant for `params` on the uploaded scene (1 untimed + 2 timed launches each,
+ * into internal scratch images, synchronous) and keeps the fastest for launches of that shape. */
+rt_status rt_tune(rt_context* ctx, const rt_frame_params* params, rt_tuning* out /* nullable */);
+/* What rt_render would run for `params` now, and what is known about the variants. params == NULL:
+ * the variant the LAST launch of this context ran (kernel = RT_KERNEL_LITERAL when the scene or the
+ * flags sent it to the literal kernel).                                                          */
+rt_status rt_get_tuning(rt_context* ctx, const rt_frame_params* params, rt_tuning* out);
+/* Pins kernel / registers / phase_level for every later launch (fields < 0 = leave to the library);
+ * NULL removes the pin.                                                                          */
+rt_status rt_set_tuning(rt_context* ctx, const rt_tuning* tuning);
+/* on = 0: rt_render never times variants on the caller's launches (untuned shapes run the default
+ * variant until rt_tune is called). Default: on.                                                */
+rt_status rt_set_autotune(rt_context* ctx, int on);
 
 /* Introspection of the host-side scene staging (no CUDA call, no context): builds the light grids
  * rt_upload_scene would build for these records (large scenes only) into

@@ -35,8 +35,11 @@ EXPORTED_SYMBOLS = [
     "rt_set_skybox", "rt_set_noise", "rt_render", "rt_render_host", "rt_synchronize", "rt_render_gl",
     "rt_get_counters", "rt_set_host_path", "rt_device_alloc", "rt_device_free", "rt_ipc_export",
     "rt_ipc_open", "rt_ipc_close", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
-    "rt_debug_light_grids",
+    "rt_debug_light_grids", "rt_tune", "rt_get_tuning", "rt_set_tuning", "rt_set_autotune",
 ]
+KERNEL_AUTO, KERNEL_MEGAKERNEL, KERNEL_WAVEFRONT, KERNEL_LITERAL = -1, 0, 1, 2
+TUNING_DEFAULT, TUNING_TRIALS, TUNING_CHOSEN, TUNING_PINNED = range(4)
+KERNEL_NAMES = {-1: "auto", 0: "megakernel", 1: "wavefront", 2: "literal"}
 POST_EXPORTED_SYMBOLS = [                   # include/rt_post.h
     "rt_generate_aabbs", "rt_generate_aabbs_device", "rt_decode_rgbe", "rt_equirect_to_cubemap",
     "rt_bloom_extract", "rt_gaussian_blur", "rt_bloom_combine", "rt_taa_resolve", "rt_post_chain", "rt_post_launch_count",
@@ -48,6 +51,13 @@ FRAME_EXPORTED_SYMBOLS = [                  # include/rt_frame.h
     "rt_frame_render_host", "rt_frame_launch_count",
 ]
 DISPLAY_RGBA32F, DISPLAY_RGBA8 = 0, 1
+MULTI_EXPORTED_SYMBOLS = [                  # include/rt_multi.h
+    "rt_multi_create", "rt_multi_destroy", "rt_multi_last_error", "rt_multi_size", "rt_multi_context", "rt_multi_upload_scene",
+    "rt_multi_set_skybox", "rt_multi_set_noise", "rt_multi_render", "rt_multi_synchronize", "rt_multi_render_host",
+    "rt_multi_launch_count", "rt_peer_reduce", "rt_peer_reduce_status",
+]
+MULTI_ROWS, MULTI_SAMPLES = 0, 1
+RT_MAX_PEERS, RT_PEER_FLAG_WORDS = 16, 64
 
 
 class RtLibraryError(RuntimeError):
@@ -74,6 +84,31 @@ class FrameParams(C.Structure):
         ("frame_count", C.c_int32), ("num_samples", C.c_int32), ("max_ray_depth", C.c_int32),
         ("flags", C.c_uint32),
         ("row_band", C.c_int32), ("row_period", C.c_int32), ("row_phase", C.c_int32),
+    ]
+
+
+class Tuning(C.Structure):
+    """rt_tuning (include/rt_abi.h): which build of the pass runs, and what was measured."""
+    _fields_ = [
+        ("kernel", C.c_int32), ("registers", C.c_int32), ("phase_level", C.c_int32), ("state", C.c_int32),
+        ("num_variants", C.c_int32), ("variant_ms", C.c_float * 8),
+        ("variant_kernel", C.c_int32 * 8), ("variant_registers", C.c_int32 * 8), ("variant_phase_level", C.c_int32 * 8),
+    ]
+
+    def as_dict(self) -> dict:
+        return {"kernel": KERNEL_NAMES.get(self.kernel, str(self.kernel)), "registers": 80 if self.registers else 128,
+                "phase_level": self.phase_level, "state": ("default", "trials", "chosen", "pinned")[self.state],
+                "variants": [{"kernel": KERNEL_NAMES.get(self.variant_kernel[i], "?"), "registers": 80 if self.variant_registers[i] else 128,
+                              "phase_level": self.variant_phase_level[i], "ms": round(float(self.variant_ms[i]), 4)}
+                             for i in range(self.num_variants)]}
+
+
+class PeerReduceDesc(C.Structure):
+    """rt_peer_reduce_desc (include/rt_multi.h)."""
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32),
+        ("partial", C.c_void_p * 16), ("result", C.c_void_p), ("flags", C.c_void_p * 16),
+        ("pixels", C.c_uint64), ("scale", C.c_float), ("epoch", C.c_uint32),
     ]
 
 
@@ -137,6 +172,10 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_launch_count.restype = C.c_uint64
     lib.rt_debug_light_grids.argtypes = [vp, ip, vp, ip, vp, C.c_size_t, C.POINTER(ip), C.POINTER(ip), vp]
     lib.rt_debug_light_grids.restype = C.c_size_t
+    lib.rt_tune.argtypes = [vp, C.POINTER(FrameParams), C.POINTER(Tuning)]
+    lib.rt_get_tuning.argtypes = [vp, C.POINTER(FrameParams), C.POINTER(Tuning)]
+    lib.rt_set_tuning.argtypes = [vp, C.POINTER(Tuning)]
+    lib.rt_set_autotune.argtypes = [vp, ip]
     # include/rt_post.h
     pp = C.POINTER(PostParams)
     lib.rt_generate_aabbs.argtypes = [vp, vp, ip]
@@ -161,6 +200,25 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_frame_render_host.argtypes = [vp, fp, pp, vp, ip, vp, ip, vp, ip]
     lib.rt_frame_launch_count.argtypes = [vp]
     lib.rt_frame_launch_count.restype = C.c_uint64
+    # include/rt_multi.h
+    lib.rt_multi_create.argtypes = [C.POINTER(vp), C.POINTER(ip), ip]
+    lib.rt_multi_destroy.argtypes = [vp]
+    lib.rt_multi_destroy.restype = None
+    lib.rt_multi_last_error.argtypes = [vp]
+    lib.rt_multi_last_error.restype = C.c_char_p
+    lib.rt_multi_size.argtypes = [vp]
+    lib.rt_multi_context.argtypes = [vp, ip]
+    lib.rt_multi_context.restype = vp
+    lib.rt_multi_upload_scene.argtypes = [vp, vp, ip, vp, ip]
+    lib.rt_multi_set_skybox.argtypes = [vp, vp, ip, ip, ip]
+    lib.rt_multi_set_noise.argtypes = [vp, vp, ip, ip]
+    lib.rt_multi_render.argtypes = [vp, fp, ip, vp, vp, vp, vp]
+    lib.rt_multi_synchronize.argtypes = [vp]
+    lib.rt_multi_render_host.argtypes = [vp, fp, ip, vp, ip, vp, ip, vp, vp, vp, vp]
+    lib.rt_multi_launch_count.argtypes = [vp]
+    lib.rt_multi_launch_count.restype = C.c_uint64
+    lib.rt_peer_reduce.argtypes = [vp, C.POINTER(PeerReduceDesc), vp]
+    lib.rt_peer_reduce_status.argtypes = [vp, vp]
     if path is None:
         _lib = lib
     return lib

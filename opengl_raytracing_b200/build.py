@@ -23,9 +23,11 @@ UNITS = [  # (source, extra flags)
     ("rt_post.cu", ["-fmad=false"]),
     ("rt_frame.cu", ["-fmad=false"]),
     ("rt_peak.cu", []),
+    ("rt_multi.cu", []),
 ]
-HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
-           os.path.join("..", "..", "include", "rt_post.h"), os.path.join("..", "..", "include", "rt_frame.h")]
+HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_wavefront.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
+           os.path.join("..", "..", "include", "rt_post.h"), os.path.join("..", "..", "include", "rt_frame.h"),
+           os.path.join("..", "..", "include", "rt_multi.h")]
 
 
 def _stale(target: str, deps: list) -> bool:
@@ -41,20 +43,30 @@ def build(force: bool = False, verbose: bool = False, variant: str = "", defines
     hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
     objs, rebuilt = [], False
     lib = LIB if not variant else LIB[:-3] + variant + ".so"
+    jobs = []
     for src, extra in UNITS:
         s = os.path.join(CSRC, src)
         o = s[:-3] + variant + ".o"
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
-            cmd = [NVCC] + ARCH + COMMON + extra + [f"-D{d}" for d in defines] + ["-c", s, "-o", o]
-            r = subprocess.run(cmd, capture_output=True, text=True)
-            with open(o + ".log", "w") as f:
-                f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
-            if verbose or r.returncode != 0:
-                sys.stderr.write(r.stdout + r.stderr)
-            if r.returncode != 0:
-                raise RuntimeError(f"nvcc failed on {src}")
-            rebuilt = True
+            jobs.append((src, o, [NVCC] + ARCH + COMMON + extra + [f"-D{d}" for d in defines] + ["-c", s, "-o", o]))
+
+    def compile_one(job):
+        src, o, cmd = job
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        with open(o + ".log", "w") as f:
+            f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+        return src, r
+
+    if jobs:                                  # the translation units compile side by side
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 1)) as ex:
+            for src, r in ex.map(compile_one, jobs):
+                if verbose or r.returncode != 0:
+                    sys.stderr.write(r.stdout + r.stderr)
+                if r.returncode != 0:
+                    raise RuntimeError(f"nvcc failed on {src}")
+        rebuilt = True
     if force or rebuilt or _stale(lib, objs):
         cmd = [NVCC] + ARCH + ["-shared", "-o", lib] + objs
         subprocess.run(cmd, check=True)

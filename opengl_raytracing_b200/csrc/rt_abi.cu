@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include <cuda_fp16.h>
+#include <nvtx3/nvToolsExt.h>
 #include "rt_device.h"
 
 namespace rt {
@@ -35,26 +36,51 @@ struct rt_context {
   // textures
   uint2* d_sky = nullptr; cudaArray_t sky_array = nullptr; cudaTextureObject_t sky_tex = 0; int sky_size = 0;
   unsigned char* d_noise = nullptr; int noise_w = 0, noise_h = 0;
-  // work distribution + counters
-  unsigned* d_tile_counter = nullptr; unsigned tile_base = 0;
+  // work distribution + counters. Every launch takes the next of kCounterSlots work counters (each
+  // monotonically increasing, 128 B apart); a slot is reused only behind the event its previous
+  // launch recorded, so launches that overlap on different streams never share a counter.
+  static constexpr int kCounterSlots = 16;
+  unsigned* d_tile_counter = nullptr;
+  struct CounterSlot { unsigned base = 0; cudaEvent_t done = nullptr; bool used = false; } slots[kCounterSlots];
+  int next_slot = 0;
   unsigned long long* d_counters = nullptr;
   uint64_t launches = 0;
   // e2e path
   int host_path = RT_HOST_PATH_AUTO;
   int coherent_override = -1;   // RT_PK_COHERENT=0..3 pins the phase level (both kernels)
-  // Large-scene kernel: 128-register (2 CTAs/SM) vs 80-register (3 CTAs/SM) build, each with independent
-  // warps or CTA-coherent phases (level 3) — four variants, identical images. Which is fastest depends
-  // on the scene (B200: C3 32.9 ms independent/128, 19.3 ms coherent/80; C5 10.7 ms independent/128,
-  // 12.5 ms coherent/80). Auto: frame 1 of a new (scene shape, frame shape) runs untimed, the next
-  // frames time one variant each with events on the caller's stream, the frame after reads the
-  // times and keeps the fastest.
+  // Kernel variants with identical images (rt_packet.cuh): the large-scene kernel exists at 128 registers
+  // (2 CTAs/SM) and 80 registers (3 CTAs/SM), each with independent warps or CTA-coherent phases; which is
+  // fastest depends on the scene (B200: C3 coherent, C5 independent). The choice per (scene shape, launch
+  // shape) is made once — by rt_tune, or (autotune on, the default) on the launches after the first of a new
+  // shape, each variant timed kTuneTrials times with events on the caller's stream — and kept in a small
+  // table, so launches of different shapes (the bands of the BANDED host path) do not evict each other.
   int dense_override = -1;      // RT_PK_DENSE=0/1 pins the register budget
   int fan_override = -1;        // dev A/B: RT_PK_FAN=0 disables the analytic PCSS probe classification of the fast build
   int grid_override = -1;       // dev A/B: RT_PK_GRID=0 disables the light grids of large scenes
   // light grids (build_light_grids): cached while the uploaded bytes do not change (the reference re-uploads every frame)
   std::vector<unsigned char> grid_key; std::vector<float4> grid_data; int grid_off_f4 = 0, grid_ent_f4 = 0;
   size_t off_grid = 0, grid_f4s = 0;
-  struct Tune { long long key[8] = {-1, 0, 0, 0, 0, 0, 0, 0}; int state = 0; int choice = 0; cudaEvent_t ev[4][2] = {}; } tune;
+  static constexpr int kTuneTrials = 2, kTuneVariants = 8, kTuneEntries = 8;
+  struct Variant { int kernel, dense, coherent; };          // kernel: RT_KERNEL_*
+  struct TuneEntry {
+    long long key[10] = {-1, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int nv = 0; Variant v[kTuneVariants] = {};
+    int state = 0;                 // 0 new, 1..nv*kTuneTrials trials issued, then chosen
+    int choice = 0; bool chosen = false;
+    float ms[kTuneVariants] = {};  // best trial of each variant (0 = not measured)
+    cudaEvent_t ev[kTuneVariants][kTuneTrials][2] = {};
+    uint64_t last_use = 0;
+  };
+  std::vector<TuneEntry> tune;
+  bool autotune = true;
+  bool pinned = false; Variant pin = {0, 0, 0};
+  int last_kernel = -1, last_dense = 0, last_coherent = 0;
+  uint64_t tune_clock = 0;
+  int wavefront_override = -1;  // RT_PK_WAVEFRONT=0 removes the wavefront pipeline from the variants, 1 pins it
+  void* wf_state = nullptr;     // wavefront queues (rt_wavefront.cuh), sized on first use
+  size_t wf_bytes = 0;
+  cudaEvent_t wf_done = nullptr;
+  size_t wf_chunk_pixels = (size_t)1 << 21;   // RT_WF_CHUNK: pixels per wavefront chunk (queue memory ~ 300 B per pixel)
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t band_done[16] = {};
   cudaStream_t stream = nullptr;
@@ -74,12 +100,16 @@ rt_status cuda_fail(rt_context* c, cudaError_t e, const char* what) {
   rt_status s = (e == cudaErrorMemoryAllocation) ? RT_ERR_OOM : RT_ERR_CUDA;
   return fail(c, s, std::string(what) + ": " + cudaGetErrorString(e));
 }
+void release_tune_events(rt_context::TuneEntry& t) {
+  for (auto& v : t.ev) for (auto& k : v) for (auto& e : k) if (e) { cudaEventDestroy(e); e = nullptr; }
+}
 }  // namespace
 
 namespace rt {
 int ctx_device(rt_context* c) { return c->device; }
 rt_status ctx_fail(rt_context* c, rt_status s, const std::string& msg) { return fail(c, s, msg); }
 void** ctx_post_slot(rt_context* c) { return &c->post_state; }
+void ctx_count_launch(rt_context* c) { c->launches += 1; }
 }  // namespace rt
 
 namespace {
@@ -517,8 +547,10 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if ((e = cudaSetDevice(cuda_device)) != cudaSuccess) return bail(e);
   if ((e = cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, cuda_device)) != cudaSuccess) return bail(e);
   if ((e = cudaDeviceGetAttribute(&c->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cuda_device)) != cudaSuccess) return bail(e);
-  if ((e = cudaMalloc(&c->d_tile_counter, sizeof(unsigned))) != cudaSuccess) return bail(e);
-  if ((e = cudaMemset(c->d_tile_counter, 0, sizeof(unsigned))) != cudaSuccess) return bail(e);
+  if ((e = cudaMalloc(&c->d_tile_counter, sizeof(unsigned) * 32 * rt_context::kCounterSlots)) != cudaSuccess) return bail(e);
+  if ((e = cudaMemset(c->d_tile_counter, 0, sizeof(unsigned) * 32 * rt_context::kCounterSlots)) != cudaSuccess) return bail(e);
+  for (auto& sl : c->slots)
+    if ((e = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)) != cudaSuccess) return bail(e);
   if ((e = cudaMalloc(&c->d_counters, sizeof(unsigned long long) * RT_CNT_COUNT)) != cudaSuccess) return bail(e);
   if ((e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * RT_CNT_COUNT)) != cudaSuccess) return bail(e);
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e);
@@ -538,6 +570,9 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if (const char* e3 = getenv("RT_PK_DENSE")) c->dense_override = atoi(e3);
   if (const char* e4 = getenv("RT_PK_FAN")) c->fan_override = atoi(e4);
   if (const char* e5 = getenv("RT_PK_GRID")) c->grid_override = atoi(e5);
+  if (const char* e6 = getenv("RT_PK_WAVEFRONT")) c->wavefront_override = atoi(e6);
+  if (const char* e8 = getenv("RT_WF_CHUNK")) c->wf_chunk_pixels = (size_t)atoll(e8) > 0 ? (size_t)atoll(e8) : c->wf_chunk_pixels;
+  if (const char* e7 = getenv("RT_AUTOTUNE")) c->autotune = atoi(e7) != 0;
   *out = c;
   return RT_OK;
 }
@@ -547,11 +582,13 @@ void rt_destroy(rt_context* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   rt::post_release(c->post_state);
-  for (int i = 0; i < 4; ++i) for (int j = 0; j < 2; ++j) if (c->tune.ev[i][j]) cudaEventDestroy(c->tune.ev[i][j]);
+  for (auto& t : c->tune) release_tune_events(t);
+  for (auto& sl : c->slots) if (sl.done) cudaEventDestroy(sl.done);
   if (c->sky_tex) cudaDestroyTextureObject(c->sky_tex);
   if (c->sky_array) cudaFreeArray(c->sky_array);
   cudaFree(c->d_sky); cudaFree(c->d_noise); cudaFree(c->d_scene);
-  cudaFree(c->d_tile_counter); cudaFree(c->d_counters);
+  cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->wf_state);
+  if (c->wf_done) cudaEventDestroy(c->wf_done);
   cudaFree(c->o_color); cudaFree(c->o_position); cudaFree(c->o_normal); cudaFree(c->o_id);
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->stage_done) cudaEventDestroy(c->stage_done);
@@ -688,9 +725,29 @@ rt_status rt_set_noise(rt_context* c, const unsigned char* r8, int w, int h) {
   return RT_OK;
 }
 
-rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, float* d_position, void* d_normal,
-                    int32_t* d_object_id, void* cuda_stream) {
-  if (!c || !p) return RT_ERR_INVALID_ARG;
+// ---- variant table (rt_context::TuneEntry)
+static void fill_tuning(const rt_context* c, const rt_context::TuneEntry* t, rt_context::Variant run, int state, rt_tuning* out) {
+  std::memset(out, 0, sizeof(*out));
+  out->kernel = run.kernel; out->registers = run.dense; out->phase_level = run.coherent; out->state = state;
+  if (!t) return;
+  out->num_variants = t->nv;
+  for (int i = 0; i < t->nv && i < 8; ++i) {
+    out->variant_ms[i] = t->ms[i]; out->variant_kernel[i] = t->v[i].kernel;
+    out->variant_registers[i] = t->v[i].dense; out->variant_phase_level[i] = t->v[i].coherent;
+  }
+  (void)c;
+}
+
+// Everything rt_render decides before it launches: validated arguments -> KernelParams, whether the packet
+// kernel can take the scene, the variants that apply, and the table entry of this launch shape.
+struct LaunchPlan {
+  rt::KernelParams kp;
+  bool use_packet = false, par = false, skip = false;
+  int nv = 0; rt_context::Variant v[rt_context::kTuneVariants];
+  long long key[10];
+};
+
+static rt_status plan_launch(rt_context* c, const rt_frame_params* p, LaunchPlan& L) {
   if (p->width <= 0 || p->height <= 0 || p->row_begin < 0 || p->row_end > p->height || p->row_begin > p->row_end)
     return fail(c, RT_ERR_INVALID_ARG, "rt_render: image size / row window");
   if (p->num_objects < 0 || p->num_objects > c->n_obj || p->num_lights < 0 || p->num_lights > c->n_lights)
@@ -699,9 +756,8 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   if (p->use_skybox && !c->d_sky) return fail(c, RT_ERR_INVALID_ARG, "rt_render: use_skybox without rt_set_skybox");
   if (p->row_band < 0 || (p->row_band > 0 && (p->row_band % 4 != 0 || p->row_period <= 0 || p->row_phase < 0 || p->row_phase >= p->row_period)))
     return fail(c, RT_ERR_INVALID_ARG, "rt_render: row_band must be a multiple of 4, 0 <= row_phase < row_period");
-  if (p->row_begin == p->row_end) return RT_OK;
-  RT_CUDA(c, cudaSetDevice(c->device));
-  rt::KernelParams kp;
+  if (p->row_begin == p->row_end) { L.skip = true; return RT_OK; }
+  rt::KernelParams& kp = L.kp;
   std::memset(&kp, 0, sizeof(kp));
   kp.fp = *p;
   kp.tan_fov = std::tan(p->fov_deg * 0.017453292519943295f * 0.5f);   // tan(radians(fov) * 0.5), glsl:209
@@ -714,14 +770,12 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   sc.scene_in_smem = smem <= (size_t)c->max_smem_optin - 2048 ? 1 : 0;
   sc.sky = c->d_sky; sc.sky_tex = (unsigned long long)c->sky_tex; sc.sky_size = c->sky_size;
   sc.noise = c->d_noise; sc.noise_w = c->noise_w; sc.noise_h = c->noise_h;
-  kp.color = (float4*)d_color; kp.position = (float4*)d_position; kp.normal = d_normal; kp.object_id = d_object_id;
-  kp.tile_counter = c->d_tile_counter; kp.tile_base = c->tile_base;
   kp.tiles_x = (unsigned)((p->width + 7) / 8);
   int local_rows = p->row_end - p->row_begin;
   if (p->row_band > 0) {                                   // rows of the bands this caller owns
     const int nbands = (local_rows + p->row_band - 1) / p->row_band;
     const int mine = nbands > p->row_phase ? (nbands - p->row_phase + p->row_period - 1) / p->row_period : 0;
-    if (mine == 0) return RT_OK;
+    if (mine == 0) { L.skip = true; return RT_OK; }
     local_rows = mine * p->row_band;                       // the last band may be cut by row_end (checked per pixel)
   }
   kp.tiles_y = (unsigned)((local_rows + 3) / 4);
@@ -732,9 +786,9 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   // one (counters need its reference-literal loops), renders a prefix of the uploaded arrays
   // (the packet blob is staged for the full scene), or the scene does not fit shared memory.
   const bool full_scene = p->num_objects == c->n_obj && p->num_lights == c->n_lights;
-  const bool use_packet = !(p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) && full_scene && c->pk_float4s > 0 &&
-                          c->pk_float4s * sizeof(float4) + 32 * 1024 * 2 <= (size_t)c->max_smem_optin - 1024;
-  sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = use_packet ? (int)c->pk_float4s : 0;
+  L.use_packet = !(p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) && full_scene && c->pk_float4s > 0 &&
+                 rt::packet_smem_bytes((int)c->pk_float4s) <= (size_t)c->max_smem_optin - 1024;
+  sc.pk_blob = c->d_scene + c->off_pk; sc.pk_float4s = L.use_packet ? (int)c->pk_float4s : 0;
   sc.pk_num_spheres = c->pk_spheres; sc.pk_num_planes = c->pk_planes; sc.pk_lights_offset = c->pk_lights_offset;
   sc.pk_num_clusters = c->pk_clusters;
   sc.pk_material_offset = c->pk_material_offset;
@@ -743,63 +797,281 @@ rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, flo
   // CTA-coherent phases pay off while the per-ray object loop is short (instruction-fetch bound);
   // with long loops the barrier imbalance costs more than the fetch locality gains.
   sc.pk_big = c->pk_spheres + c->pk_planes > 48 ? 1 : 0;
-  // small-scene kernel only: barrier per block (1), + per bounce (2), + per light (3). Measured on B200: with
-  // bounces the finer phases win slightly (C2 0.4366 / 0.4341 / 0.4318 ms), a single-bounce frame has too
-  // few phases for the barriers to pay (C1 0.1033 / 0.1053 / 0.1074 ms).
-  sc.pk_coherent = c->coherent_override >= 0 ? c->coherent_override : (p->max_ray_depth <= 1 ? 1 : 3);
-  const bool par = (p->flags & RT_FLAG_PARITY_MATH) != 0u;
-  // ---- variant choice for the large-scene kernel (see rt_context::Tune)
-  sc.pk_dense = 0;
-  int timed = -1;                                          // >= 0: this launch is a timed trial of that variant
-  if (use_packet && sc.pk_big) {
-    rt_context::Tune& t = c->tune;
-    int vd[4], vc[4], nv = 0;                              // candidate (register budget, phase level) pairs
-    for (int coh = 0; coh <= 3; coh += 3)
-      for (int dense = 0; dense <= 1; ++dense) {
-        if (c->dense_override >= 0 && dense != (c->dense_override ? 1 : 0)) continue;
-        if (c->coherent_override >= 0 && coh != 0) continue;
-        vd[nv] = dense; vc[nv] = c->coherent_override >= 0 ? c->coherent_override : coh; ++nv;
-      }
-    int pick = 0;
-    if (nv > 1) {
-      const long long key[8] = {c->pk_spheres, c->pk_planes, c->n_lights, p->width, (long long)kp.tiles_y, p->max_ray_depth,
-                                p->num_samples, (long long)(par ? 1 : 0) | ((long long)(p->row_band > 0) << 1) | ((long long)nv << 2)};
-      if (std::memcmp(key, t.key, sizeof(key)) != 0) { std::memcpy(t.key, key, sizeof(key)); t.state = 0; t.choice = 0; }
-      if (t.state == 0) {                                  // first frame: untimed (cold caches, module load)
-        if (!t.ev[0][0]) for (int i = 0; i < 4; ++i) for (int j = 0; j < 2; ++j) RT_CUDA(c, cudaEventCreate(&t.ev[i][j]));
-        t.state = 1;
-      } else if (t.state <= nv) {
-        timed = t.state - 1; pick = timed; t.state += 1;
-      } else if (t.state == nv + 1) {                      // every trial is at least one frame old
-        float best = 0.0f;
-        int arg = 0;
-        for (int i = 0; i < nv; ++i) {
-          float ms = 0.0f;
-          const bool ok = cudaEventSynchronize(t.ev[i][1]) == cudaSuccess && cudaEventElapsedTime(&ms, t.ev[i][0], t.ev[i][1]) == cudaSuccess;
-          if (!ok) { cudaGetLastError(); arg = 0; break; }
-          if (i == 0 || ms < best) { best = ms; arg = i; }
+  L.par = (p->flags & RT_FLAG_PARITY_MATH) != 0u;
+  // ---- the variants that apply (identical images; see rt_context::TuneEntry). v[0] is the default.
+  L.nv = 0;
+  if (L.use_packet) {
+    if (!sc.pk_big) {
+      // small scenes: barrier per block (1), + per bounce (2), + per light (3). Measured on B200: with bounces the
+      // finer phases win slightly (C2 0.4366 / 0.4341 / 0.4318 ms), a single-bounce frame has too few phases for
+      // the barriers to pay (C1 0.1033 / 0.1053 / 0.1074 ms).
+      const int coh = c->coherent_override >= 0 ? c->coherent_override : (p->max_ray_depth <= 1 ? 1 : 3);
+      L.v[L.nv++] = {RT_KERNEL_MEGAKERNEL, 0, coh};
+    } else {
+      for (int coh = 3; coh >= 0; coh -= 3)
+        for (int dense = 0; dense <= 1; ++dense) {
+          if (c->dense_override >= 0 && dense != (c->dense_override ? 1 : 0)) continue;
+          if (c->coherent_override >= 0 && coh != 3) continue;
+          L.v[L.nv++] = {RT_KERNEL_MEGAKERNEL, dense, c->coherent_override >= 0 ? c->coherent_override : coh};
         }
-        t.choice = arg;
-        t.state = nv + 2;
-        pick = t.choice;
-      } else {
-        pick = t.choice;
+    }
+    if (rt::wavefront_supported(kp) && c->wavefront_override != 0) {
+      if (c->wavefront_override == 1) L.nv = 0;            // RT_PK_WAVEFRONT=1 pins it
+      L.v[L.nv++] = {RT_KERNEL_WAVEFRONT, 0, 0};
+    }
+  }
+  const long long key[10] = {c->pk_spheres, c->pk_planes, c->n_lights, p->width, p->height, local_rows, p->max_ray_depth, p->num_samples,
+                             (long long)(L.par ? 1 : 0) | ((long long)L.nv << 2) | ((long long)p->row_band << 8) | ((long long)p->row_period << 24),
+                             (long long)(p->use_skybox ? 1 : 0) | ((long long)(p->flags & RT_FLAG_SKYBOX_HW) << 1)};
+  std::memcpy(L.key, key, sizeof(key));
+  return RT_OK;
+}
+
+static rt_context::TuneEntry* find_tune(rt_context* c, const LaunchPlan& L, bool create) {
+  for (auto& t : c->tune)
+    if (std::memcmp(t.key, L.key, sizeof(L.key)) == 0) { t.last_use = ++c->tune_clock; return &t; }
+  if (!create) return nullptr;
+  if ((int)c->tune.size() >= rt_context::kTuneEntries) {   // evict the least recently used shape
+    size_t lru = 0;
+    for (size_t i = 1; i < c->tune.size(); ++i) if (c->tune[i].last_use < c->tune[lru].last_use) lru = i;
+    release_tune_events(c->tune[lru]);
+    c->tune.erase(c->tune.begin() + (long)lru);
+  }
+  c->tune.emplace_back();
+  rt_context::TuneEntry& t = c->tune.back();
+  std::memcpy(t.key, L.key, sizeof(L.key));
+  t.nv = L.nv;
+  for (int i = 0; i < L.nv; ++i) t.v[i] = L.v[i];
+  t.last_use = ++c->tune_clock;
+  return &t;
+}
+
+// Applies a pin (rt_set_tuning) to the variant list: the first variant matching every pinned field.
+static int pinned_variant(const rt_context* c, const LaunchPlan& L) {
+  for (int i = 0; i < L.nv; ++i) {
+    if (c->pin.kernel >= 0 && L.v[i].kernel != c->pin.kernel) continue;
+    if (L.v[i].kernel == RT_KERNEL_MEGAKERNEL) {
+      if (c->pin.dense >= 0 && L.kp.sc.pk_big && L.v[i].dense != c->pin.dense) continue;
+      if (c->pin.coherent >= 0 && L.kp.sc.pk_big && L.v[i].coherent != c->pin.coherent) continue;
+    }
+    return i;
+  }
+  return 0;
+}
+
+// The wavefront pipeline for plan L (rt_wavefront.cuh): per chunk of tile rows and per sample, 2 D + 1 launches
+// over the context's queue buffers. Asynchronous on `stream`; renders of one context that use the queues are
+// ordered behind each other by an event.
+static rt_status wavefront_render(rt_context* c, LaunchPlan& L, cudaStream_t stream) {
+  const rt::KernelParams& kp = L.kp;
+  const int nl = kp.sc.num_lights, D = kp.fp.max_ray_depth, nsamp = kp.fp.num_samples > 0 ? kp.fp.num_samples : 1;
+  const unsigned per_row = kp.tiles_x * 32u;
+  unsigned rows_per_chunk = (unsigned)(c->wf_chunk_pixels / per_row);
+  if (rows_per_chunk < 1u) rows_per_chunk = 1u;
+  if (rows_per_chunk > kp.tiles_y) rows_per_chunk = kp.tiles_y;
+  const size_t cap = (size_t)rows_per_chunk * per_row;
+  const size_t planes = 2 * 3 + 2 * 2 + 2 * (size_t)(nl > 0 ? nl : 1);
+  const size_t acc_bytes = nsamp > 1 ? (size_t)kp.fp.width * kp.fp.height * sizeof(float4) : 0;
+  const size_t need = planes * cap * sizeof(float4) + (size_t)(nl > 0 ? nl : 1) * cap * sizeof(unsigned) + acc_bytes + rt::kWfCounters * sizeof(unsigned) + 1024;
+  if (need > c->wf_bytes) {
+    RT_CUDA(c, cudaDeviceSynchronize());
+    cudaFree(c->wf_state); c->wf_state = nullptr; c->wf_bytes = 0;
+    RT_CUDA(c, cudaMalloc(&c->wf_state, need));
+    c->wf_bytes = need;
+  }
+  if (!c->wf_done) RT_CUDA(c, cudaEventCreateWithFlags(&c->wf_done, cudaEventDisableTiming));
+  else RT_CUDA(c, cudaStreamWaitEvent(stream, c->wf_done, 0));
+  rt::WfParams wp;
+  std::memset(&wp, 0, sizeof(wp));
+  float4* f = (float4*)c->wf_state;
+  wp.path[0] = f; f += 3 * cap; wp.path[1] = f; f += 3 * cap;
+  wp.hit[0] = f; f += 2 * cap; wp.hit[1] = f; f += 2 * cap;
+  wp.brdf[0] = f; f += (size_t)(nl > 0 ? nl : 1) * cap; wp.brdf[1] = f; f += (size_t)(nl > 0 ? nl : 1) * cap;
+  wp.acc = nsamp > 1 ? f : nullptr; f += acc_bytes / sizeof(float4);
+  wp.jobq = (unsigned*)f;
+  wp.counters = wp.jobq + (size_t)(nl > 0 ? nl : 1) * cap;
+  wp.cap = (unsigned)cap;
+  for (unsigned row0 = 0; row0 < kp.tiles_y; row0 += rows_per_chunk) {
+    wp.tile_row0 = row0;
+    wp.tile_rows = kp.tiles_y - row0 < rows_per_chunk ? kp.tiles_y - row0 : rows_per_chunk;
+    for (int sidx = 0; sidx < nsamp; ++sidx) {
+      wp.sample = sidx;
+      RT_CUDA(c, cudaMemsetAsync(wp.counters, 0, rt::kWfCounters * sizeof(unsigned), stream));
+      for (int d = 0; d <= D; ++d) {
+        wp.depth = d;
+        cudaError_t e = L.par ? rt::launch_wf_bounce_parity(kp, wp, c->sm_count, stream) : rt::launch_wf_bounce_fast(kp, wp, c->sm_count, stream);
+        if (e != cudaSuccess) return cuda_fail(c, e, "wavefront bounce launch");
+        c->launches += 1;
+        if (d == D || nl == 0) continue;
+        e = L.par ? rt::launch_wf_shadow_parity(kp, wp, c->sm_count, stream) : rt::launch_wf_shadow_fast(kp, wp, c->sm_count, stream);
+        if (e != cudaSuccess) return cuda_fail(c, e, "wavefront shadow launch");
+        c->launches += 1;
       }
     }
-    sc.pk_dense = vd[pick];
-    sc.pk_coherent = vc[pick];
   }
-  unsigned warps = 0;
+  RT_CUDA(c, cudaEventRecord(c->wf_done, stream));
+  return RT_OK;
+}
+
+// One launch of variant `v` (or the literal kernel) of plan L on `stream`.
+static rt_status launch_variant(rt_context* c, LaunchPlan& L, rt_context::Variant v, float* d_color, float* d_position, void* d_normal,
+                                int32_t* d_object_id, cudaStream_t stream) {
+  rt::KernelParams& kp = L.kp;
+  kp.color = (float4*)d_color; kp.position = (float4*)d_position; kp.normal = d_normal; kp.object_id = d_object_id;
+  rt_context::CounterSlot& slot = c->slots[c->next_slot];
+  if (slot.used) RT_CUDA(c, cudaStreamWaitEvent(stream, slot.done, 0));   // a no-op when the previous user ran on this stream
+  kp.tile_counter = c->d_tile_counter + 32 * c->next_slot; kp.tile_base = slot.base;
+  kp.sc.pk_dense = v.dense; kp.sc.pk_coherent = v.coherent;
+  unsigned advance = 0;
   cudaError_t e;
-  if (timed >= 0) RT_CUDA(c, cudaEventRecord(c->tune.ev[timed][0], (cudaStream_t)cuda_stream));
-  if (use_packet) e = par ? rt::launch_packet_parity(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps)
-                          : rt::launch_packet_fast(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps);
-  else e = par ? rt::launch_render_parity(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps)
-               : rt::launch_render_fast(kp, c->sm_count, (cudaStream_t)cuda_stream, &warps);
+  if (L.use_packet && v.kernel == RT_KERNEL_WAVEFRONT) {
+    rt_status st = wavefront_render(c, L, stream);
+    if (st != RT_OK) return st;
+    e = cudaSuccess;
+  } else if (L.use_packet) {
+    e = L.par ? rt::launch_packet_parity(kp, c->sm_count, stream, &advance) : rt::launch_packet_fast(kp, c->sm_count, stream, &advance);
+    c->launches += 1;
+  } else {
+    e = L.par ? rt::launch_render_parity(kp, c->sm_count, stream, &advance) : rt::launch_render_fast(kp, c->sm_count, stream, &advance);
+    c->launches += 1;
+  }
   if (e != cudaSuccess) return cuda_fail(c, e, "rt_render launch");
-  if (timed >= 0) RT_CUDA(c, cudaEventRecord(c->tune.ev[timed][1], (cudaStream_t)cuda_stream));
-  c->tile_base += kp.tiles_x * kp.tiles_y + warps;   // unsigned wrap-around is intended     // tiles + the over-fetch the launcher reports (one per warp / CTA round)
-  c->launches += 1;
+  slot.base += kp.tiles_x * kp.tiles_y + advance;   // tiles + the over-fetch the launcher reports; unsigned wrap-around is intended
+  RT_CUDA(c, cudaEventRecord(slot.done, stream));
+  slot.used = true;
+  c->next_slot = (c->next_slot + 1) % rt_context::kCounterSlots;
+  c->last_kernel = L.use_packet ? v.kernel : RT_KERNEL_LITERAL; c->last_dense = v.dense; c->last_coherent = v.coherent;
+  return RT_OK;
+}
+
+// Reads the finished trials of an entry and fixes its choice.
+static void conclude_tune(rt_context::TuneEntry& t) {
+  int arg = 0; float best = 0.0f; bool ok = true;
+  for (int i = 0; i < t.nv && ok; ++i) {
+    float vbest = 0.0f;
+    for (int k = 0; k < rt_context::kTuneTrials; ++k) {
+      float ms = 0.0f;
+      if (cudaEventSynchronize(t.ev[i][k][1]) != cudaSuccess || cudaEventElapsedTime(&ms, t.ev[i][k][0], t.ev[i][k][1]) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+      if (k == 0 || ms < vbest) vbest = ms;
+    }
+    t.ms[i] = vbest;
+    if (i == 0 || vbest < best) { best = vbest; arg = i; }
+  }
+  t.choice = ok ? arg : 0;
+  t.chosen = true;
+}
+
+rt_status rt_render(rt_context* c, const rt_frame_params* p, float* d_color, float* d_position, void* d_normal,
+                    int32_t* d_object_id, void* cuda_stream) {
+  if (!c || !p) return RT_ERR_INVALID_ARG;
+  LaunchPlan L;
+  rt_status st = plan_launch(c, p, L);
+  if (st != RT_OK || L.skip) return st;
+  RT_CUDA(c, cudaSetDevice(c->device));
+  nvtxRangePushA("rt_render");
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  rt_context::Variant run = L.nv ? L.v[0] : rt_context::Variant{RT_KERNEL_LITERAL, 0, 0};
+  int trial = -1, trial_k = 0;
+  rt_context::TuneEntry* t = nullptr;
+  if (L.nv > 1 && c->pinned) run = L.v[pinned_variant(c, L)];
+  else if (L.nv > 1) {
+    t = find_tune(c, L, c->autotune);
+    if (t && t->chosen) run = t->v[t->choice];
+    else if (t && c->autotune) {
+      // launch 1 of a new shape runs the default untimed (cold caches, module load); the next nv * kTuneTrials
+      // launches are timed trials (variant-major), the one after reads the events and fixes the choice
+      const int total = t->nv * rt_context::kTuneTrials;
+      if (t->state == 0) t->state = 1;
+      else if (t->state <= total) {
+        trial = (t->state - 1) / rt_context::kTuneTrials; trial_k = (t->state - 1) % rt_context::kTuneTrials;
+        for (int j = 0; j < 2; ++j)
+          if (!t->ev[trial][trial_k][j]) { cudaError_t e = cudaEventCreate(&t->ev[trial][trial_k][j]); if (e != cudaSuccess) { nvtxRangePop(); return cuda_fail(c, e, "cudaEventCreate"); } }
+        run = t->v[trial];
+        t->state += 1;
+      } else { conclude_tune(*t); run = t->v[t->choice]; }
+    }
+  }
+  if (trial >= 0) cudaEventRecord(t->ev[trial][trial_k][0], stream);
+  st = launch_variant(c, L, run, d_color, d_position, d_normal, d_object_id, stream);
+  if (trial >= 0) cudaEventRecord(t->ev[trial][trial_k][1], stream);
+  nvtxRangePop();
+  return st;
+}
+
+rt_status rt_tune(rt_context* c, const rt_frame_params* p, rt_tuning* out) {
+  if (!c || !p) return RT_ERR_INVALID_ARG;
+  LaunchPlan L;
+  rt_status st = plan_launch(c, p, L);
+  if (st != RT_OK) return st;
+  if (L.skip || L.nv <= 1) {
+    if (out) fill_tuning(c, nullptr, L.nv ? L.v[0] : rt_context::Variant{RT_KERNEL_LITERAL, 0, 0}, RT_TUNING_CHOSEN, out);
+    return RT_OK;
+  }
+  RT_CUDA(c, cudaSetDevice(c->device));
+  st = ensure_outputs(c, (size_t)p->width * p->height);
+  if (st != RT_OK) return st;
+  rt_context::TuneEntry* t = find_tune(c, L, true);
+  cudaEvent_t e0, e1;
+  RT_CUDA(c, cudaEventCreate(&e0)); RT_CUDA(c, cudaEventCreate(&e1));
+  const bool acc = (p->flags & RT_FLAG_ACCUMULATE) != 0u;
+  for (int i = 0; i < t->nv && st == RT_OK; ++i) {
+    float best = 0.0f;
+    for (int k = 0; k <= rt_context::kTuneTrials && st == RT_OK; ++k) {           // k = 0: untimed
+      if (acc) cudaMemsetAsync(c->o_color, 0, (size_t)p->width * p->height * sizeof(float4), c->stream);
+      cudaEventRecord(e0, c->stream);
+      st = launch_variant(c, L, t->v[i], (float*)c->o_color, (float*)c->o_position, c->o_normal, nullptr, c->stream);
+      cudaEventRecord(e1, c->stream);
+      if (st != RT_OK) break;
+      float ms = 0.0f;
+      if (cudaEventSynchronize(e1) != cudaSuccess || cudaEventElapsedTime(&ms, e0, e1) != cudaSuccess) { st = cuda_fail(c, cudaGetLastError(), "rt_tune"); break; }
+      if (k == 1 || (k > 1 && ms < best)) best = ms;
+    }
+    t->ms[i] = best;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (st != RT_OK) return st;
+  int arg = 0;
+  for (int i = 1; i < t->nv; ++i) if (t->ms[i] < t->ms[arg]) arg = i;
+  t->choice = arg; t->chosen = true; t->state = t->nv * rt_context::kTuneTrials + 2;
+  if (out) fill_tuning(c, t, t->v[arg], RT_TUNING_CHOSEN, out);
+  return RT_OK;
+}
+
+rt_status rt_get_tuning(rt_context* c, const rt_frame_params* p, rt_tuning* out) {
+  if (!c || !out) return RT_ERR_INVALID_ARG;
+  if (!p) {
+    fill_tuning(c, nullptr, rt_context::Variant{c->last_kernel, c->last_dense, c->last_coherent}, RT_TUNING_DEFAULT, out);
+    return RT_OK;
+  }
+  LaunchPlan L;
+  rt_status st = plan_launch(c, p, L);
+  if (st != RT_OK) return st;
+  if (L.skip || L.nv == 0) { fill_tuning(c, nullptr, rt_context::Variant{RT_KERNEL_LITERAL, 0, 0}, RT_TUNING_DEFAULT, out); return RT_OK; }
+  rt_context::TuneEntry* t = L.nv > 1 ? find_tune(c, L, false) : nullptr;
+  if (L.nv > 1 && c->pinned) fill_tuning(c, t, L.v[pinned_variant(c, L)], RT_TUNING_PINNED, out);
+  else if (t && t->chosen) fill_tuning(c, t, t->v[t->choice], RT_TUNING_CHOSEN, out);
+  else if (t && t->state > 0) fill_tuning(c, t, L.v[0], RT_TUNING_TRIALS, out);
+  else fill_tuning(c, t, L.v[0], RT_TUNING_DEFAULT, out);
+  if (!t) {                                                // report the applicable variants even when nothing is measured
+    out->num_variants = L.nv;
+    for (int i = 0; i < L.nv && i < 8; ++i) { out->variant_kernel[i] = L.v[i].kernel; out->variant_registers[i] = L.v[i].dense; out->variant_phase_level[i] = L.v[i].coherent; }
+  }
+  return RT_OK;
+}
+
+rt_status rt_set_tuning(rt_context* c, const rt_tuning* tuning) {
+  if (!c) return RT_ERR_INVALID_ARG;
+  if (!tuning) { c->pinned = false; return RT_OK; }
+  if (tuning->kernel > RT_KERNEL_WAVEFRONT || tuning->registers > 1 || tuning->phase_level > 3)
+    return fail(c, RT_ERR_INVALID_ARG, "rt_set_tuning: kernel / registers / phase_level out of range");
+  c->pinned = true;
+  c->pin = {tuning->kernel, tuning->registers, tuning->phase_level};
+  return RT_OK;
+}
+
+rt_status rt_set_autotune(rt_context* c, int on) {
+  if (!c) return RT_ERR_INVALID_ARG;
+  c->autotune = on != 0;
   return RT_OK;
 }
 

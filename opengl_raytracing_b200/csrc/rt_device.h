@@ -79,6 +79,40 @@ struct KernelParams {
 };
 
 size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights);
+// ---- wavefront pipeline (rt_wavefront.cuh): the same pass as three kinds of launches over compacted
+// queues in global memory instead of one persistent megakernel. Per sample and per chunk of tile rows:
+//   bounce(0) shadow(0) bounce(1) shadow(1) ... bounce(D-1) shadow(D-1) bounce(D)
+// bounce(d): shades the hits of depth d-1 from their (BRDF term, shadow factor) records, applies Russian
+//            roulette, builds the next ray, traces it (closest hit), finishes the pixels whose path ended, and
+//            pushes the surviving hits — compacted with warp ballots — into the hit queue of depth d together
+//            with one (BRDF term) record per light and one shadow job per light that needs rays;
+// shadow(d): one lane per shadow job (shading point x light), light by light: the cone-culled packets of
+//            rt_packet.cuh, writing the job's shadow factor next to its BRDF term.
+// Every kernel has its own register budget; every lane of a warp has work. Queue planes are SoA float4.
+constexpr int kWfMaxDepth = 16, kWfMaxLights = 32;
+constexpr int kWfCounters = 64 + 2 * (kWfMaxDepth + 1) * kWfMaxLights;
+__host__ __device__ inline int wf_c_work(int d) { return d; }                                   // work cursor of bounce(d)
+__host__ __device__ inline int wf_c_nq(int d) { return 32 + d; }                                // hits pushed by bounce(d)
+__host__ __device__ inline int wf_c_jobn(int d, int l) { return 64 + d * kWfMaxLights + l; }    // shadow jobs of (d, light)
+__host__ __device__ inline int wf_c_jobcur(int d, int l) { return 64 + (kWfMaxDepth + 1 + d) * kWfMaxLights + l; }
+struct WfParams {
+  float4* path[2];           // ping-pong, 3 planes each: (rd, pixel bits) (throughput, noise_r) (colour, 0); [k * cap + slot]
+  float4* hit[2];            // ping-pong, 2 planes each: (P, object index bits) (N, contributing-light mask bits)
+  float4* brdf[2];           // ping-pong, num_lights planes each: (BRDF term of the light, shadow factor)
+  unsigned* jobq;            // num_lights planes: hit-queue slot of each shadow job
+  float4* acc;               // full-frame running colour sum of a multi-sample render (num_samples > 1), else null
+  unsigned* counters;        // kWfCounters, zeroed before every (chunk, sample)
+  unsigned cap;              // slots per plane
+  int depth;                 // this launch: bounce(depth) / shadow(depth)
+  int sample;                // 0 .. num_samples-1
+  unsigned tile_row0, tile_rows;   // the chunk: tile rows [tile_row0, tile_row0 + tile_rows) of the launch window
+};
+bool wavefront_supported(const KernelParams& kp);
+size_t packet_smem_bytes(int pk_float4s);   // dynamic shared memory of the packet / wavefront kernels for a blob of that size
+cudaError_t launch_wf_bounce_fast(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
+cudaError_t launch_wf_bounce_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
+cudaError_t launch_wf_shadow_fast(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
+cudaError_t launch_wf_shadow_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
 
 // One launcher per (variant) translation unit: rt_kernel_fast.cu is compiled with FMA
 // contraction, rt_kernel_parity.cu with -fmad=false and IEEE-only arithmetic.
@@ -98,6 +132,7 @@ cudaError_t upload_tables_parity(const float* halton2, const float* halton3, con
 int ctx_device(rt_context* c);
 rt_status ctx_fail(rt_context* c, rt_status s, const std::string& msg);
 void** ctx_post_slot(rt_context* c);
+void ctx_count_launch(rt_context* c);   // rt_launch_count bookkeeping for kernels launched outside rt_abi.cu
 void post_release(void* state);
 
 }  // namespace rt

@@ -4,6 +4,7 @@
 #define RT_VARIANT_NS parity
 #include "rt_kernel.cuh"
 #include "rt_packet.cuh"
+#include "rt_wavefront.cuh"
 
 namespace rt {
 cudaError_t launch_render_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
@@ -16,5 +17,11 @@ cudaError_t upload_tables_parity(const float* halton2, const float* halton3, con
   cudaError_t e = parity::upload_tables(halton2, halton3);
   if (e != cudaSuccess) return e;
   return parity::pk::upload_probe_order(halton3, probe_order);
+}
+cudaError_t launch_wf_bounce_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream) {
+  return parity::pk::launch_wf_bounce(kp, wp, sm_count, stream);
+}
+cudaError_t launch_wf_shadow_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream) {
+  return parity::pk::launch_wf_shadow(kp, wp, sm_count, stream);
 }
 }  // namespace rt

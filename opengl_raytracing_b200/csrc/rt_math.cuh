@@ -192,17 +192,22 @@ __device__ __forceinline__ float halton(int index, int base) {
   return result;
 }
 
-// cosineWeightedHemisphere (glsl:291-308)
-__device__ __forceinline__ f3 cosine_hemisphere(float rx, float ry, f3 normal) {
+// cosineWeightedHemisphere (glsl:291-308). Its result is the diffuse-bounce (and SSS) ray DIRECTION, i.e. part of
+// the geometric chain ray -> t -> P -> N: IEEE square roots and normalisation in both builds, and sin / cos
+// evaluated in FP64 and rounded (like random2 below): sincosf is 2 ulp off, and every curved mirror after a
+// diffuse bounce multiplies that by ~2 * distance / radius. Out of line: it runs once per diffuse bounce, and
+// scenes without diffuse materials (the shipped ones) keep it out of their instruction stream and registers.
+__device__ __noinline__ f3 cosine_hemisphere(float rx, float ry, f3 normal) {
   const float phi = 2.0f * kPi * rx;
-  const float cosTheta = sqrt_shade(ry);
-  const float sinTheta = sqrt_shade(1.0f - ry);
-  float sp, cp;
-  sincosf(phi, &sp, &cp);
+  const float cosTheta = sqrt_ieee(ry);
+  const float sinTheta = sqrt_ieee(1.0f - ry);
+  double sd, cd;
+  sincos((double)phi, &sd, &cd);
+  const float sp = (float)sd, cp = (float)cd;
   const f3 h = mk3(sinTheta * cp, cosTheta, sinTheta * sp);
-  const f3 tangent = normalize_shade(cross3(normal, mk3(0.0f, 1.0f, 1.0f)));
+  const f3 tangent = normalize_ieee(cross3(normal, mk3(0.0f, 1.0f, 1.0f)));
   const f3 bitangent = cross3(normal, tangent);
-  return normalize_shade(tangent * h.x + bitangent * h.z + normal * h.y);
+  return normalize_ieee(tangent * h.x + bitangent * h.z + normal * h.y);
 }
 
 // Halton tables for the fixed-index call sites (PCF i<pcfSamples bases 2,3; PCSS i<16 base 3),

@@ -117,6 +117,29 @@ class RtContext:
     def launch_count(self) -> int:
         return int(self.lib.rt_launch_count(self.handle))
 
+    # kernel variants (identical images): rt_tune / rt_get_tuning / rt_set_tuning / rt_set_autotune
+    def tune(self, params: abi.FrameParams) -> dict:
+        t = abi.Tuning()
+        self._check(self.lib.rt_tune(self.handle, C.byref(params), C.byref(t)))
+        return t.as_dict()
+
+    def get_tuning(self, params: abi.FrameParams | None = None) -> dict:
+        t = abi.Tuning()
+        self._check(self.lib.rt_get_tuning(self.handle, C.byref(params) if params is not None else None, C.byref(t)))
+        return t.as_dict()
+
+    def set_tuning(self, kernel: int | None = None, registers: int = -1, phase_level: int = -1) -> None:
+        """kernel None removes the pin; fields < 0 are left to the library."""
+        if kernel is None:
+            self._check(self.lib.rt_set_tuning(self.handle, None))
+            return
+        t = abi.Tuning()
+        t.kernel, t.registers, t.phase_level = kernel, registers, phase_level
+        self._check(self.lib.rt_set_tuning(self.handle, C.byref(t)))
+
+    def set_autotune(self, on: bool) -> None:
+        self._check(self.lib.rt_set_autotune(self.handle, 1 if on else 0))
+
 
 def frame_params(width: int, height: int, num_objects: int, num_lights: int, camera: S.Camera | None = None,
                  max_ray_depth: int = 3, frame_count: int = 0, num_samples: int = 1, use_skybox: bool = False,
@@ -151,6 +174,67 @@ def workload_params(w, flags: int = 0, **over) -> abi.FrameParams:
               num_samples=w.num_samples, use_skybox=w.use_skybox, flags=flags)
     kw.update(over)
     return frame_params(**kw)
+
+
+class MultiGpu:
+    """``rt_multi`` (include/rt_multi.h): one process driving several GPUs of the box — row bands stored straight
+    into the root GPU's images over NVLink, or sample ranges summed by the peer pull-reduce kernel."""
+
+    def __init__(self, devices):
+        self.lib = abi.load_library()
+        self.handle = C.c_void_p(0)
+        self.devices = list(devices)
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        st = self.lib.rt_multi_create(C.byref(self.handle), arr, len(self.devices))
+        if st != abi.RT_OK:
+            raise abi.RtError(st, "rt_multi_create failed: " + self.lib.rt_status_string(st).decode())
+        self._keep = {}
+
+    def _check(self, st: int) -> None:
+        if st != abi.RT_OK:
+            raise abi.RtError(st, (self.lib.rt_multi_last_error(self.handle) or b"").decode() or self.lib.rt_status_string(st).decode())
+
+    def bind_workload(self, w) -> None:
+        objects = np.ascontiguousarray(w.objects, dtype=S.OBJECT_DTYPE)
+        lights = np.ascontiguousarray(w.lights, dtype=S.LIGHT_DTYPE)
+        self._keep["scene"] = (objects, lights)
+        self._check(self.lib.rt_multi_upload_scene(self.handle, _ptr(objects), len(objects), _ptr(lights), len(lights)))
+        if w.use_skybox and w.skybox is not None:
+            faces = np.ascontiguousarray(w.skybox)
+            self._check(self.lib.rt_multi_set_skybox(self.handle, _ptr(faces), faces.shape[1], faces.shape[3], 1 if faces.dtype == np.float16 else 0))
+        else:
+            self._check(self.lib.rt_multi_set_skybox(self.handle, None, 0, 0, 0))
+        if w.noise is None:
+            self._check(self.lib.rt_multi_set_noise(self.handle, None, 0, 0))
+        else:
+            noise = np.ascontiguousarray(w.noise, dtype=np.uint8)
+            self._check(self.lib.rt_multi_set_noise(self.handle, _ptr(noise), noise.shape[1], noise.shape[0]))
+
+    def render(self, params: abi.FrameParams, sharding: int, color=None, position=None, normal=None, object_id=None) -> None:
+        self._check(self.lib.rt_multi_render(self.handle, C.byref(params), sharding, _ptr(color), _ptr(position), _ptr(normal), _ptr(object_id)))
+
+    def synchronize(self) -> None:
+        self._check(self.lib.rt_multi_synchronize(self.handle))
+
+    def render_host(self, params: abi.FrameParams, sharding: int, objects, lights, color, position, normal, object_id=None) -> None:
+        n = 0 if objects is None else len(objects)
+        m = 0 if lights is None else len(lights)
+        self._check(self.lib.rt_multi_render_host(self.handle, C.byref(params), sharding, _ptr(objects), n, _ptr(lights), m,
+                                                  _ptr(color), _ptr(position), _ptr(normal), _ptr(object_id)))
+
+    def launch_count(self) -> int:
+        return int(self.lib.rt_multi_launch_count(self.handle))
+
+    def close(self) -> None:
+        if self.handle:
+            self.lib.rt_multi_destroy(self.handle)
+            self.handle = C.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 # --------------------------------------------------------------------------- reference-named mirror

@@ -142,3 +142,97 @@ class PeerFrame:
             else:
                 self.ctx.lib.rt_ipc_close(self.ctx.handle, p)
         self.ptr = {}
+
+
+class PeerReducer:
+    """The sample-range exchange step without NCCL (one process per GPU): every rank's partial-sum frame, rank 0's
+    result frame and a block of flag words per rank are CUDA-IPC mapped into every rank; ``reduce`` enqueues ONE
+    kernel (rt_peer_reduce, include/rt_multi.h) that signals "my partial is complete", waits for every peer, sums
+    this rank's slice of all partials in rank order (deterministic), scales, and stores it into rank 0's frame.
+    Two partial buffers alternate between consecutive reduces (a rank may render the next frame while a peer
+    still reads its partial of this one): render into ``partial`` (the buffer of the NEXT reduce), then call
+    ``reduce``. ``result`` on rank 0 = the finished mean frame."""
+
+    FLAG_BYTES = 2 << 20          # its own 2 MB allocation: CUDA IPC handles map whole allocations
+
+    def __init__(self, ctx, height: int, width: int, group=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        from . import abi
+        self.ctx, self.h, self.w, self.group = ctx, height, width, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        assert self.world <= abi.RT_MAX_PEERS
+        self.epoch = 0
+        nbytes = height * width * 16
+        names = ["partial0", "partial1", "flags"] + (["result"] if self.rank == 0 else [])
+        self.own, handles = {}, torch.zeros(4, 64, dtype=torch.uint8)
+        for i, name in enumerate(names):
+            p = C.c_void_p(0)
+            ctx._check(ctx.lib.rt_device_alloc(ctx.handle, C.byref(p), self.FLAG_BYTES if name == "flags" else nbytes))
+            buf = C.create_string_buffer(64)
+            ctx._check(ctx.lib.rt_ipc_export(ctx.handle, p, buf))
+            self.own[name] = p.value
+            handles[i] = torch.tensor(list(buf.raw), dtype=torch.uint8)
+        dev = torch.device("cpu") if dist.get_backend(group) == "gloo" else torch.device("cuda", ctx.device)
+        mine = handles.to(dev)
+        torch.cuda.set_device(ctx.device)
+        zero = torch.as_tensor(_DevicePtr(self.own["flags"], (self.FLAG_BYTES // 4,), "<u4"), device=f"cuda:{ctx.device}")
+        zero.view(torch.int32).zero_()
+        torch.cuda.synchronize(ctx.device)
+        everyone = [torch.zeros_like(mine) for _ in range(self.world)]
+        dist.all_gather(everyone, mine, group=group)
+        self.maps = []                       # per rank: {name: device address valid in THIS process}
+        self._opened = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.maps.append(dict(self.own))
+                continue
+            hb = everyone[r].cpu().numpy()
+            m = {}
+            for i, name in enumerate(["partial0", "partial1", "flags"] + (["result"] if r == 0 else [])):
+                p = C.c_void_p(0)
+                ctx._check(ctx.lib.rt_ipc_open(ctx.handle, hb[i].tobytes(), C.byref(p)))
+                m[name] = p.value
+                self._opened.append(p.value)
+            self.maps.append(m)
+        dist.barrier(group=group)            # every flag block is zeroed and mapped before the first epoch
+
+    def _tensor(self, ptr):
+        import torch
+        return torch.as_tensor(_DevicePtr(ptr, (self.h, self.w, 4), "<f4"), device=f"cuda:{self.ctx.device}")
+
+    @property
+    def partial(self):
+        """The buffer this rank renders its partial sum of the NEXT reduce into (a torch view)."""
+        return self._tensor(self.own["partial%d" % ((self.epoch + 1) & 1)])
+
+    @property
+    def result(self):
+        assert self.rank == 0
+        return self._tensor(self.own["result"])
+
+    def reduce(self, stream: int, total_samples: int) -> None:
+        import ctypes as C
+        from . import abi
+        self.epoch += 1
+        d = abi.PeerReduceDesc()
+        d.rank, d.world = self.rank, self.world
+        for r in range(self.world):
+            d.partial[r] = self.maps[r]["partial%d" % (self.epoch & 1)]
+            d.flags[r] = self.maps[r]["flags"]
+        d.result = self.maps[0]["result"]
+        d.pixels, d.scale, d.epoch = self.h * self.w, 1.0 / float(total_samples), self.epoch
+        self.ctx._check(self.ctx.lib.rt_peer_reduce(self.ctx.handle, C.byref(d), C.c_void_p(stream)))
+
+    def check(self) -> None:
+        """After a synchronise: raises if a wait inside an earlier reduce kernel timed out."""
+        import ctypes as C
+        self.ctx._check(self.ctx.lib.rt_peer_reduce_status(self.ctx.handle, C.c_void_p(self.own["flags"])))
+
+    def close(self):
+        for p in self._opened:
+            self.ctx.lib.rt_ipc_close(self.ctx.handle, p)
+        for p in self.own.values():
+            self.ctx.lib.rt_device_free(self.ctx.handle, p)
+        self._opened, self.own = [], {}

@@ -69,6 +69,9 @@ def load(kind: str = "port") -> C.CDLL:
     lib.oracle_render.argtypes = [C.POINTER(abi.FrameParams), vp, vp, vp, ip, vp, ip, ip,
                                   ip, ip, ip, ip, ip, ip, vp, vp, vp, vp, vp, ip]
     lib.oracle_render.restype = ip
+    if kind == "port":
+        lib.oracle_render_margins.argtypes = lib.oracle_render.argtypes + [vp]
+        lib.oracle_render_margins.restype = ip
     assert lib.oracle_kind().decode() == kind
     _libs[kind] = lib
     return lib
@@ -93,10 +96,13 @@ def _sky_f32(sky: np.ndarray | None):
 
 
 def render(w, kind: str = "port", x0: int = 0, y0: int = 0, sx: int = 1, sy: int = 1,
-           nx: int | None = None, ny: int | None = None, threads: int = 0, params: abi.FrameParams | None = None):
+           nx: int | None = None, ny: int | None = None, threads: int = 0, params: abi.FrameParams | None = None,
+           margins: bool = False):
     """Runs one of the CPU oracles on a ``synthetic.Workload``. Renders pixels
     (x0+i*sx, y0+j*sy); default = the full frame. Returns a dict of (ny,nx,4) float32 arrays
-    ``color``/``position``/``normal`` (row 0 = gl y 0) and ``counters``."""
+    ``color``/``position``/``normal`` (row 0 = gl y 0) and ``counters``. ``margins`` (port only) adds
+    ``margin`` (ny,nx): the smallest relative margin of any geometric decision on the pixel's path
+    (rt_oracle.cpp margin_of_object) — what tests/parity.py classifies grazing pixels with."""
     lib = load(kind)
     p = params or workload_params(w)
     if nx is None:
@@ -112,17 +118,26 @@ def render(w, kind: str = "port", x0: int = 0, y0: int = 0, sx: int = 1, sy: int
     lights = np.ascontiguousarray(w.lights)
     sky = _sky_f32(w.skybox) if w.use_skybox else None
     noise = None if w.noise is None else np.ascontiguousarray(w.noise, dtype=np.uint8)
-    rc = lib.oracle_render(
-        C.byref(p), objects.ctypes.data, lights.ctypes.data,
-        None if sky is None else sky.ctypes.data, 0 if sky is None else sky.shape[1],
-        None if noise is None else noise.ctypes.data,
-        0 if noise is None else noise.shape[1], 0 if noise is None else noise.shape[0],
-        x0, y0, sx, sy, nx, ny, color.ctypes.data, position.ctypes.data, normal.ctypes.data, object_id.ctypes.data,
-        C.cast(counters, C.c_void_p), threads)
+    args = [C.byref(p), objects.ctypes.data, lights.ctypes.data,
+            None if sky is None else sky.ctypes.data, 0 if sky is None else sky.shape[1],
+            None if noise is None else noise.ctypes.data,
+            0 if noise is None else noise.shape[1], 0 if noise is None else noise.shape[0],
+            x0, y0, sx, sy, nx, ny, color.ctypes.data, position.ctypes.data, normal.ctypes.data, object_id.ctypes.data,
+            C.cast(counters, C.c_void_p), threads]
+    margin = None
+    if margins:
+        assert kind == "port", "grazing margins come from the instrumented port (bit-identical to the reference build)"
+        margin = np.full((ny, nx), np.inf, np.float32)
+        rc = lib.oracle_render_margins(*args, margin.ctypes.data)
+    else:
+        rc = lib.oracle_render(*args)
     if rc != 0:
         raise RuntimeError(f"oracle_render({kind}) failed: {rc}")
-    return {"color": color, "position": position, "normal": normal, "object_id": object_id,
-            "counters": {k: int(counters[i]) for i, k in enumerate(abi.COUNTER_NAMES)}}
+    out = {"color": color, "position": position, "normal": normal, "object_id": object_id,
+           "counters": {k: int(counters[i]) for i, k in enumerate(abi.COUNTER_NAMES)}}
+    if margin is not None:
+        out["margin"] = margin
+    return out
 
 
 # --------------------------------------------------------------------------- f1-f3 stages (post_api.h)

@@ -186,6 +186,46 @@ bool intersectPlane(const Ray& ray, const rt_object& obj, float& t, bool* full) 
   return false;
 }
 
+// ---- grazing margin (test instrumentation, does not touch the rendering arithmetic). While a pixel's
+// margin is tracked (oracle_margins), every closest-hit ray of its path (primary and bounce rays — the calls
+// that pass hitIndex) records the smallest RELATIVE margin by which one of its geometric decisions was taken:
+//   sphere      |disc| / max(b^2, |4ac|)                      the hit/miss decision of glsl:112
+//   rectangle   | |x| - size/2 | / (size/2), same for z        the in-rectangle decision of glsl:147 (t >= 0 only)
+//               (both only for objects whose hit, or near miss, would lie in front of the closest hit)
+//   ordering    (t2 - t1) / t2 of the two nearest hits         the closest-hit decision of glsl:178
+// A pixel whose object id / hit mask differs between the kernel and the oracle must have a margin below the
+// stated epsilon (tests/parity.py GRAZING_EPS): that is the "stated grazing-angle pixels" set of north_star.
+thread_local float* tl_margin = nullptr;
+inline void margin_min(float v) { if (tl_margin && v == v && v < *tl_margin) *tl_margin = v; }
+// limit = the closest hit found (or maxRayDistance): an object whose near-miss lies beyond it decides nothing.
+void margin_of_object(const Ray& ray, const rt_object& obj, float limit) {
+  if (obj.type == 0) {
+    V3 oc = sub(ray.origin, ld3(obj.position));
+    float a = dot3(ray.direction, ray.direction);
+    float bq = 2.0f * dot3(oc, ray.direction);
+    float c = dot3(oc, oc) - obj.radius * obj.radius;
+    float disc = bq * bq - 4.0f * a * c;
+    float den = std::fmax(bq * bq, std::fabs(4.0f * a * c));
+    // spheres behind the ray, or whose closest approach lies beyond the closest hit, decide nothing
+    if (den > 0.0f && bq < 0.0f && -bq / (2.0f * a) <= limit * 1.001f) margin_min(std::fabs(disc) / den);
+  } else if (obj.type == 1) {
+    V3 n = ld3(obj.normal);
+    float denom = dot3(n, ray.direction);
+    if (!(std::fabs(denom) > 1e-6f)) return;
+    float t = dot3(sub(ld3(obj.position), ray.origin), n) / denom;
+    if (!(t >= 0.0f) || !(t <= limit * 1.001f)) return;
+    V3 right = std::fabs(n.y) > 0.9f ? normalize3(cross3(n, mk(0.f, 0.f, 1.f))) : normalize3(cross3(n, mk(0.f, 1.f, 0.f)));
+    V3 forward = normalize3(cross3(right, n));
+    V3 local = sub(add(ray.origin, scale(ray.direction, t)), ld3(obj.position));
+    float hx = obj.size[0] / 2.0f, hz = obj.size[1] / 2.0f;
+    float mx = std::fabs(std::fabs(dot3(local, right)) - hx) / std::fmax(hx, 1e-30f);
+    float mz = std::fabs(std::fabs(dot3(local, forward)) - hz) / std::fmax(hz, 1e-30f);
+    // only the coordinate that decides: inside in the other one
+    if (std::fabs(dot3(local, forward)) <= hz * 1.001f) margin_min(mx);
+    if (std::fabs(dot3(local, right)) <= hx * 1.001f) margin_min(mz);
+  }
+}
+
 // intersectObjects (glsl:155-196): closest hit over ALL objects in array order, strict
 // `<` (first object wins ties). On a miss *mat and *N are left untouched.
 bool intersectObjects(const Bindings& b, Counters& k, const Ray& ray, const rt_material** mat, V3* N, float* tOut,
@@ -193,6 +233,8 @@ bool intersectObjects(const Bindings& b, Counters& k, const Ray& ray, const rt_m
   float minT = b.maxRayDistance;
   bool hit = false;
   k.c[RT_CNT_RAYS]++;
+  const bool track = tl_margin && hitIndex;
+  float t1 = INFINITY, t2 = INFINITY;                       // the two nearest hits (instrumentation only)
   for (int i = 0; i < b.numObjects; ++i) {
     const rt_object& obj = b.objects[i];
     k.c[RT_CNT_AABB]++;
@@ -207,6 +249,9 @@ bool intersectObjects(const Bindings& b, Counters& k, const Ray& ray, const rt_m
       isHit = intersectPlane(ray, obj, currentT, &full);
       k.c[full ? RT_CNT_PLANE_FULL : RT_CNT_PLANE_EARLY]++;
     }
+    if (track && isHit && currentT > 0.0f) {
+      if (currentT < t1) { t2 = t1; t1 = currentT; } else if (currentT < t2) t2 = currentT;
+    }
     if (isHit && currentT > 0.0f && currentT < minT) {
       minT = currentT;
       hit = true;
@@ -220,6 +265,10 @@ bool intersectObjects(const Bindings& b, Counters& k, const Ray& ray, const rt_m
         *N = ld3(obj.normal);
       }
     }
+  }
+  if (track) {
+    if (t2 < INFINITY) margin_min((t2 - t1) / t2);
+    for (int i = 0; i < b.numObjects; ++i) margin_of_object(ray, b.objects[i], minT);
   }
   *tOut = minT;
   return hit;
@@ -499,13 +548,14 @@ void shade_pixel(const Bindings& b, Counters& k, unsigned px, unsigned py, Pixel
 
 extern "C" const char* oracle_kind(void) { return "port"; }
 
-extern "C" int oracle_render(const rt_frame_params* p, const void* objects, const void* lights,
-                             const float* sky_rgba32f, int face_size,
-                             const unsigned char* noise_r8, int noise_w, int noise_h,
-                             int x0, int y0, int sx, int sy, int nx, int ny,
-                             float* color, float* position, float* normal, int32_t* object_id,
-                             uint64_t* counters, int nthreads) {
+static int render_impl(const rt_frame_params* p, const void* objects, const void* lights,
+                       const float* sky_rgba32f, int face_size,
+                       const unsigned char* noise_r8, int noise_w, int noise_h,
+                       int x0, int y0, int sx, int sy, int nx, int ny,
+                       float* color, float* position, float* normal, int32_t* object_id,
+                       uint64_t* counters, int nthreads, float* margin) {
   if (!p || !color || !position || !normal) return 1;
+  if (margin) for (size_t o = 0; o < (size_t)nx * ny; ++o) margin[o] = INFINITY;
   Bindings b;
   b.objects = (const rt_object*)objects; b.numObjects = p->num_objects;
   b.lights = (const rt_light*)lights; b.numLights = p->num_lights;
@@ -529,7 +579,9 @@ extern "C" int oracle_render(const rt_frame_params* p, const void* objects, cons
       for (int j = 0; j < ny; ++j) {
         for (int i = 0; i < nx; ++i) {
           PixelOut o;
+          tl_margin = margin ? margin + (size_t)j * nx + i : nullptr;      // min over the samples of the pixel
           shade_pixel(b, local, (unsigned)(x0 + i * sx), (unsigned)(y0 + j * sy), &o);
+          tl_margin = nullptr;
           size_t at = ((size_t)j * nx + i) * 4;
           if (s == 0) {
             for (int c = 0; c < 3; ++c) { color[at + c] = o.color[c]; position[at + c] = o.P[c]; normal[at + c] = o.N[c]; }
@@ -551,4 +603,26 @@ extern "C" int oracle_render(const rt_frame_params* p, const void* objects, cons
   }
   if (counters) for (int c = 0; c < RT_CNT_COUNT; ++c) counters[c] = total.c[c];
   return 0;
+}
+
+extern "C" int oracle_render(const rt_frame_params* p, const void* objects, const void* lights,
+                             const float* sky_rgba32f, int face_size,
+                             const unsigned char* noise_r8, int noise_w, int noise_h,
+                             int x0, int y0, int sx, int sy, int nx, int ny,
+                             float* color, float* position, float* normal, int32_t* object_id,
+                             uint64_t* counters, int nthreads) {
+  return render_impl(p, objects, lights, sky_rgba32f, face_size, noise_r8, noise_w, noise_h, x0, y0, sx, sy, nx, ny,
+                     color, position, normal, object_id, counters, nthreads, nullptr);
+}
+
+// Port only: oracle_render plus, per pixel, the grazing margin of its path (see margin_of_object); INFINITY
+// when no decision was close to anything (e.g. an empty scene).
+extern "C" int oracle_render_margins(const rt_frame_params* p, const void* objects, const void* lights,
+                                     const float* sky_rgba32f, int face_size,
+                                     const unsigned char* noise_r8, int noise_w, int noise_h,
+                                     int x0, int y0, int sx, int sy, int nx, int ny,
+                                     float* color, float* position, float* normal, int32_t* object_id,
+                                     uint64_t* counters, int nthreads, float* margin) {
+  return render_impl(p, objects, lights, sky_rgba32f, face_size, noise_r8, noise_w, noise_h, x0, y0, sx, sy, nx, ny,
+                     color, position, normal, object_id, counters, nthreads, margin);
 }

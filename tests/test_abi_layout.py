@@ -1,4 +1,4 @@
-"""C-ABI library: loads and exports every symbol include/rt_abi.h, include/rt_post.h and include/rt_frame.h declare; the ctypes
+"""C-ABI library: loads and exports every symbol include/rt_abi.h, include/rt_post.h, include/rt_frame.h and include/rt_multi.h declare; the ctypes
 structures match the header's byte layouts. No compute calls (runs without a GPU)."""
 import ctypes as C
 import os
@@ -14,6 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "rt_abi.h")
 POST_HEADER = os.path.join(ROOT, "include", "rt_post.h")
 FRAME_HEADER = os.path.join(ROOT, "include", "rt_frame.h")
+MULTI_HEADER = os.path.join(ROOT, "include", "rt_multi.h")
 
 
 def _declared_functions(header=HEADER):
@@ -27,15 +28,16 @@ def test_header_functions_match_binding_list():
     assert _declared_functions() == sorted(abi.EXPORTED_SYMBOLS)
     assert _declared_functions(POST_HEADER) == sorted(abi.POST_EXPORTED_SYMBOLS)
     assert _declared_functions(FRAME_HEADER) == sorted(abi.FRAME_EXPORTED_SYMBOLS)
+    assert _declared_functions(MULTI_HEADER) == sorted(abi.MULTI_EXPORTED_SYMBOLS)
 
 
 def test_library_loads_and_exports_every_symbol():
     from opengl_raytracing_b200 import build
     build.build()
     lib = abi.load_library()
-    for name in _declared_functions() + _declared_functions(POST_HEADER) + _declared_functions(FRAME_HEADER):
+    for name in _declared_functions() + _declared_functions(POST_HEADER) + _declared_functions(FRAME_HEADER) + _declared_functions(MULTI_HEADER):
         assert hasattr(lib, name), name
-    assert lib.rt_abi_version() == 2
+    assert lib.rt_abi_version() == 3
     assert lib.rt_status_string(5) == b"RT_ERR_UNAVAILABLE"
 
 
@@ -102,3 +104,17 @@ def test_product_never_imports_oracle():
                 text = open(os.path.join(dirpath, fn), encoding="utf-8", errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), fn
                 assert "oracle/" not in text and "oracle_api" not in text and "librt_oracle" not in text, fn
+
+
+def test_tuning_and_peer_desc_layouts_against_c_compiler(tmp_path):
+    src = tmp_path / "probe2.c"
+    body = ('printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(rt_tuning), offsetof(rt_tuning, variant_ms), '
+            'offsetof(rt_tuning, variant_phase_level), sizeof(rt_peer_reduce_desc), offsetof(rt_peer_reduce_desc, flags), '
+            'offsetof(rt_peer_reduce_desc, epoch));')
+    src.write_text('#include <stdio.h>\n#include "' + MULTI_HEADER + '"\nint main(void){' + body + 'return 0;}\n')
+    exe = tmp_path / "probe2"
+    subprocess.run(["gcc", "-std=c11", str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(abi.Tuning), abi.Tuning.variant_ms.offset, abi.Tuning.variant_phase_level.offset,
+            C.sizeof(abi.PeerReduceDesc), abi.PeerReduceDesc.flags.offset, abi.PeerReduceDesc.epoch.offset]
+    assert got == want, (got, want)

@@ -20,7 +20,7 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "gol
 
 from opengl_raytracing_b200 import abi, synthetic  # noqa: E402
 from opengl_raytracing_b200.pipeline import render_workload, workload_params, bind_workload  # noqa: E402
-from parity import compare, assert_parity  # noqa: E402
+from parity import compare, assert_parity, record  # noqa: E402
 from edge_cases import edge_workloads  # noqa: E402
 from make_golden import golden_workloads  # noqa: E402
 
@@ -32,9 +32,9 @@ SMALL = {1: (320, 180), 2: (320, 180), 3: (256, 144), 5: (256, 144)}
 @pytest.mark.parametrize("n", [1, 2, 3, 5])
 def test_config_parity_fast_variant(rt_ctx, port_oracle, n):
     w = synthetic.config(n, *SMALL[n])
-    o = port_oracle.render(w, "port")
+    o = port_oracle.render(w, "port", margins=True)
     k = render_workload(rt_ctx, w, flags=0)
-    st = compare(k, o, normal_fp16=True)
+    st = record(f"C{n} {w.width}x{w.height} fast vs port", compare(k, o, normal_fp16=True))
     assert_parity(st)
     assert (k["object_id"] >= -1).all()
 
@@ -42,13 +42,102 @@ def test_config_parity_fast_variant(rt_ctx, port_oracle, n):
 @pytest.mark.parametrize("n", [1, 2, 3, 5])
 def test_config_parity_ieee_variant_is_near_exact(rt_ctx, port_oracle, n):
     w = synthetic.config(n, *SMALL[n])
-    o = port_oracle.render(w, "port")
+    o = port_oracle.render(w, "port", margins=True)
     k = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32)
-    st = compare(k, o)
+    st = record(f"C{n} {w.width}x{w.height} parity-math vs port", compare(k, o))
+    assert_parity(st)
     assert st["id_mismatch"] <= 2 and st["hit_mismatch"] <= 2, st
     assert st["position_bad"] <= 2 and st["normal_bad"] <= 2, st
     assert st["color_bad"] <= max(2, 1e-4 * st["pixels"]), st
     assert st["color_max_abs_same_id"] < 1e-3 or st["color_bad"] <= 2, st
+
+
+def _reference_frame(oracle_mod, w, **sub):
+    """The frame (or pixel subset) as the REFERENCE BUILD renders it (oracle/_ref: the reference's own shader
+    source compiled as C++), with the object ids and grazing margins of the instrumented port — which must
+    reproduce the reference build's three images bit for bit here too, or the pin is broken."""
+    if not oracle_mod.have("reference"):
+        pytest.fail("oracle/_ref/libref_shader.so is missing on this box: build it in the container (graft build())")
+    ref = oracle_mod.render(w, "reference", **sub)
+    port = oracle_mod.render(w, "port", margins=True, **sub)
+    for key in ("color", "position", "normal"):
+        assert np.array_equal(ref[key].view(np.uint32), port[key].view(np.uint32)), ("port != reference build", w.name, key)
+    ref["object_id"], ref["margin"] = port["object_id"], port["margin"]
+    return ref
+
+
+@pytest.mark.parametrize("n", [1, 2])
+def test_metric_configs_full_frame_vs_reference_build(rt_ctx, port_oracle, n):
+    """BASELINE configs 1 and 2 at their OWN sizes (1280x720, 1920x1080), every pixel, product (fast) build and
+    parity build, against the reference build — north_star's bounds, no slack beyond them."""
+    w = synthetic.config(n)
+    assert (w.width, w.height) == ((1280, 720) if n == 1 else (1920, 1080))
+    o = _reference_frame(port_oracle, w)
+    k = render_workload(rt_ctx, w, flags=0)
+    st = record(f"C{n} full frame {w.width}x{w.height} fast vs reference build", compare(k, o, normal_fp16=True))
+    assert_parity(st)
+    k = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32, bind=False)
+    st = record(f"C{n} full frame {w.width}x{w.height} parity-math vs reference build", compare(k, o))
+    assert_parity(st)
+    assert st["color_bad"] <= 1e-5 * st["pixels"] and st["id_mismatch"] == 0 and st["position_bad"] == 0, st
+
+
+def test_config4_full_size_exact_sequence_and_converged_mean(rt_ctx, port_oracle):
+    """BASELINE config 4 at its own size: 3840x2160, 64 samples per pixel, depth 3, diffuse bounces. The kernel
+    renders the whole frame; the reference build renders every 32nd pixel in x and y (8 100 pixels x 64 samples).
+      * exact sequence: same Hammersley indices, sequential FP32 sum -> north_star's per-pixel bounds;
+      * converged mean: |mean_kernel - mean_oracle| <= 1e-3 + 3 sigma / sqrt(64) per channel, sigma =
+        the oracle's per-pixel sample standard deviation (from its 64 single-sample renders)."""
+    w = synthetic.config(4)
+    assert (w.width, w.height, w.num_samples) == (3840, 2160, 64)
+    sub = dict(x0=7, y0=11, sx=32, sy=32)
+    o = _reference_frame(port_oracle, w, **sub)
+    k = render_workload(rt_ctx, w, flags=0)
+    ks = {key: v[11::32, 7::32] for key, v in k.items()}
+    st = record("C4 3840x2160 x 64 spp fast vs reference build (every 32nd pixel)", compare(ks, o, normal_fp16=True))
+    assert_parity(st, strict_geom=False)
+    # converged mean against the per-sample statistics of the oracle
+    samples = []
+    for sidx in range(64):
+        ws = synthetic.config(4)
+        ws.num_samples, ws.frame_count = 1, w.frame_count + sidx
+        samples.append(port_oracle.render(ws, "port", **sub)["color"][..., :3].astype(np.float64))
+    samples = np.stack(samples)
+    mean, sigma = samples.mean(axis=0), samples.std(axis=0, ddof=1)
+    with np.errstate(invalid="ignore"):
+        excess = np.abs(ks["color"][..., :3].astype(np.float64) - mean) - (1e-3 + 3.0 * sigma / 8.0)
+    finite = np.isfinite(mean).all(axis=-1) & np.isfinite(ks["color"][..., :3]).all(axis=-1)
+    bad = (excess > 0).any(axis=-1) & finite
+    record("C4 converged mean (|dmean| <= 1e-3 + 3 sigma / 8)", {"pixels": int(finite.sum()), "outside": int(bad.sum()),
+           "max_excess": float(np.nanmax(np.where(finite[..., None], excess, -np.inf)))})
+    assert bad.sum() == 0, int(bad.sum())
+
+
+def test_skybox_texture_object_deviation(rt_ctx, port_oracle):
+    """RT_FLAG_SKYBOX_HW: the miss path through the CUDA cubemap TEXTURE OBJECT (north_star; glsl:531, filter state
+    src/TextureLoader.cpp:143-147) instead of the exact 4-texel FP32 filter. The hardware filter weights have 8
+    fractional bits and CUDA cubemaps filter across face edges (seamless), the reference's do not: the deviation
+    from the exact path is measured here and held to a stated bound — max and 99.9th percentile, relative to the
+    local texel contrast for the interior, absolute on the whole image."""
+    from edge_cases import edge_workloads
+    results = {}
+    for name, w in (("C2", synthetic.config(2)), ("empty_sky", edge_workloads(size=(512, 512))["empty_sky"])):
+        exact = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32)
+        hw = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32 | abi.FLAG_SKYBOX_HW, bind=False)
+        assert np.array_equal(exact["object_id"], hw["object_id"]) and np.array_equal(exact["position"], hw["position"])
+        d = np.abs(hw["color"][..., :3] - exact["color"][..., :3]).max(axis=-1)
+        scale = np.maximum(np.abs(exact["color"][..., :3]).max(axis=-1), 1.0)
+        rel = d / scale
+        results[name] = {"max_abs": float(d.max()), "p999_abs": float(np.quantile(d, 0.999)), "max_rel": float(rel.max()),
+                         "p999_rel": float(np.quantile(rel, 0.999)), "differing_frac": float((d > 0).mean())}
+        record(f"RT_FLAG_SKYBOX_HW vs exact filter, {name} {w.width}x{w.height}", dict(results[name], pixels=int(d.size)))
+        # 8-bit weights: |error| <= 2 * 2^-9 of the largest texel difference in the footprint (sun peak 40 -> 0.16);
+        # the 99.9th percentile sits on the smooth gradient, far below
+        assert results[name]["p999_rel"] <= 4e-3, results
+        assert results[name]["max_rel"] <= 5e-2, results
+    o = port_oracle.render(synthetic.config(2, 480, 270), "port", margins=True)
+    k = render_workload(rt_ctx, synthetic.config(2, 480, 270), flags=abi.FLAG_SKYBOX_HW)
+    assert_parity(record("C2 480x270 SKYBOX_HW vs port", compare(k, o, normal_fp16=True)), max_color_frac=5e-3)
 
 
 def _bits_equal(a: dict, b: dict) -> dict:
@@ -190,40 +279,38 @@ def test_config4_multisample_mean(rt_ctx, port_oracle):
     """C4 at reduced size: exact-sequence test (same Hammersley indices, sequential FP32 sum)."""
     w = synthetic.config(4, 128, 72)
     w.num_samples = 8
-    o = port_oracle.render(w, "port")
+    o = port_oracle.render(w, "port", margins=True)
     k = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32)
-    st = compare(k, o)
-    assert_parity(st, max_color_frac=3e-3)     # diffuse bounces go through sin/cos: more library-ulp pixels
+    st = record("C4 128x72 x 8 spp fast vs port", compare(k, o))
+    assert_parity(st, strict_geom=False)
 
 
-def test_golden_tiles_from_reference_build(rt_ctx):
-    """Kernel vs tiles produced by the reference's own shader source (oracle/_ref)."""
+def test_golden_tiles_from_reference_build(rt_ctx, port_oracle):
+    """Kernel (parity build) vs the committed tiles produced by the reference's own shader source (oracle/_ref);
+    object ids and grazing margins from the port, which reproduces those tiles bit for bit (tests/test_oracle.py)."""
     tiles = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tiles.npz"))
     for name, w in golden_workloads().items():
         k = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32)
-        ref_c, ref_p, ref_n = tiles[f"{name}.color"], tiles[f"{name}.position"], tiles[f"{name}.normal"]
-        hit_ref = (ref_n[..., :3] != 0).any(axis=-1)
-        hit_k = k["object_id"] >= 0
-        assert (hit_ref != hit_k).sum() <= 2, name
-        both_nan = np.isnan(k["color"]) & np.isnan(ref_c)
-        with np.errstate(invalid="ignore"):
-            d = np.where(both_nan, 0.0, np.abs(k["color"] - ref_c))
-        d = np.where(np.isnan(d), np.inf, d)
-        bad = (d[..., :3] > 1e-3).any(axis=-1)
-        assert bad.mean() <= 3e-3, (name, int(bad.sum()))
-        with np.errstate(invalid="ignore"):
-            dp = np.abs(k["position"] - ref_p).max(axis=-1)
-        assert (np.nan_to_num(dp, nan=np.inf) > 1e-3).mean() <= 3e-3, name
+        port = port_oracle.render(w, "port", margins=True)
+        ref = {"color": tiles[f"{name}.color"], "position": tiles[f"{name}.position"], "normal": tiles[f"{name}.normal"],
+               "object_id": port["object_id"], "margin": port["margin"]}
+        for key in ("color", "position", "normal"):
+            assert np.array_equal(ref[key].view(np.uint32), port[key].view(np.uint32)), (name, key)
+        st = record(f"golden tile {name} parity-math vs reference build", compare(k, ref))
+        diffuse = bool((w.objects["material"]["diffuseStrength"] > 0).any())
+        # tiles are 1.3-2.3 k pixels: 0.1 % is one or two pixels, so the colour bound is a count here
+        assert_parity(st, max_color_frac=max(1e-3, 2.5 / st["pixels"]), strict_geom=not diffuse)
 
 
 @pytest.mark.parametrize("name", sorted(edge_workloads().keys()))
 def test_edge_cases(rt_ctx, port_oracle, name):
-    w = edge_workloads()[name]
-    o = port_oracle.render(w, "port")
+    w = edge_workloads(size=(192, 128))[name]      # 24 576 pixels: 0.1 % is 24 of them
+    o = port_oracle.render(w, "port", margins=True)
+    diffuse = bool(len(w.objects) and (w.objects["material"]["diffuseStrength"] > 0).any())
     for flags in (0, abi.FLAG_PARITY_MATH):
         k = render_workload(rt_ctx, w, flags=flags | abi.FLAG_NORMAL_FP32)
-        st = compare(k, o)
-        assert_parity(st, max_color_frac=4e-3)
+        st = record(f"edge {name} {'parity-math' if flags else 'fast'} vs port", compare(k, o))
+        assert_parity(st, strict_geom=not diffuse)
         assert np.array_equal(np.isnan(k["color"]).any(axis=-1), np.isnan(o["color"]).any(axis=-1)) or st["id_mismatch"] > 0, name
 
 
@@ -328,10 +415,10 @@ def test_full_size_pixel_subset(rt_ctx, port_oracle, n):
     """BASELINE full sizes (4K / 8K): the oracle renders the fixed 1/64 pixel subset
     (every 8th pixel, offset (3,5)); the kernel renders the whole frame."""
     w = synthetic.config(n)
-    o = port_oracle.render(w, "port", x0=3, y0=5, sx=8, sy=8)
+    o = _reference_frame(port_oracle, w, x0=3, y0=5, sx=8, sy=8)
     k = render_workload(rt_ctx, w, flags=0)
     sub = {key: v[5::8, 3::8] for key, v in k.items()}
-    st = compare(sub, o, normal_fp16=True)
+    st = record(f"C{n} full size {w.width}x{w.height} fast vs reference build (every 8th pixel)", compare(sub, o, normal_fp16=True))
     assert_parity(st)
 
 
@@ -342,10 +429,10 @@ def test_shipped_scenes_at_1080p_pixel_subset(rt_ctx, port_oracle, name):
     from edge_cases import shipped_scene
     w = shipped_scene(name, (1920, 1080), 3)
     w.use_skybox, w.skybox, w.noise = True, synthetic.skybox_s1(), synthetic.noise_n1()
-    o = port_oracle.render(w, "port", x0=3, y0=5, sx=8, sy=8)
+    o = _reference_frame(port_oracle, w, x0=3, y0=5, sx=8, sy=8)
     k = render_workload(rt_ctx, w, flags=0)
     sub = {key: v[5::8, 3::8] for key, v in k.items()}
-    assert_parity(compare(sub, o, normal_fp16=True))
+    assert_parity(record(f"shipped scene {name} 1920x1080 fast vs reference build (every 8th pixel)", compare(sub, o, normal_fp16=True)))
     a = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32, bind=False)
     b = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32 | abi.FLAG_LITERAL_KERNEL, bind=False)
     assert _bits_equal(a, b) == {"color": 0, "position": 0, "normal": 0, "object_id": 0}
