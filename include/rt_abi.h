@@ -279,13 +279,19 @@ uint64_t  rt_launch_count(rt_context* ctx);
 /* Kernel variants and their tuning.                                           */
 /* The pass exists in several builds that produce IDENTICAL images (same per-pixel arithmetic,
  * different scheduling): the persistent megakernel (rt_packet.cuh) at two register budgets, with
- * independent warps or CTA-coherent phases, and the wavefront pipeline (rt_wavefront.cuh:
- * trace / shadow-job / shade kernels over compacted ray queues). Which is fastest depends on the
+ * independent warps or CTA-coherent phases, the same megakernel with the rays of a CTA regrouped
+ * between bounces and shadow jobs through shared-memory queues (rt_regroup.cuh), and the wavefront
+ * pipeline (rt_wavefront.cuh: bounce / shadow-job launches over compacted ray queues in HBM).
+ * Which is fastest depends on the
  * scene. The reference has no counterpart (one GLSL program, src/ForwardShadingPipeline.cpp:153);
  * a caller that edits the scene every frame (src/ImGUIManager.cpp:197-202) uses rt_tune once per
  * scene shape, or rt_set_tuning to pin a variant, and never renders a trial frame.            */
 /* ------------------------------------------------------------------------- */
-enum { RT_KERNEL_AUTO = -1, RT_KERNEL_MEGAKERNEL = 0, RT_KERNEL_WAVEFRONT = 1, RT_KERNEL_LITERAL = 2 };
+enum { RT_KERNEL_AUTO = -1,
+       RT_KERNEL_MEGAKERNEL = 0,   /* rt_packet.cuh: persistent, one pixel per lane for the whole path                  */
+       RT_KERNEL_WAVEFRONT  = 1,   /* rt_wavefront.cuh: bounce / shadow-job launches over compacted queues in HBM       */
+       RT_KERNEL_LITERAL    = 2,   /* rt_kernel.cuh: the reference-literal loops (counters, A/B baseline); not tunable   */
+       RT_KERNEL_REGROUP    = 3 }; /* rt_regroup.cuh: persistent, rays regrouped per CTA through shared-memory queues   */
 enum { RT_TUNING_DEFAULT = 0,    /* nothing measured for this shape: the built-in default variant  */
        RT_TUNING_TRIALS  = 1,    /* autotune is timing variants on the caller's launches            */
        RT_TUNING_CHOSEN  = 2,    /* measured (rt_tune or autotune); the fastest variant is in use   */
@@ -300,8 +306,9 @@ typedef struct rt_tuning {
   int32_t variant_kernel[8], variant_registers[8], variant_phase_level[8];
 } rt_tuning;
 
-/* Times every applicable variant for `params` on the uploaded scene (1 untimed + 2 timed launches each,
- * into internal scratch images, synchronous) and keeps the fastest for launches of that shape. */
+/* Times every applicable variant for `params` on the uploaded scene (2 timed launches each, every one enqueued
+ * behind an untimed launch so that only device time is measured; internal scratch images; synchronous) and keeps
+ * the fastest for launches of that shape. */
 rt_status rt_tune(rt_context* ctx, const rt_frame_params* params, rt_tuning* out /* nullable */);
 /* What rt_render would run for `params` now, and what is known about the variants. params == NULL:
  * the variant the LAST launch of this context ran (kernel = RT_KERNEL_LITERAL when the scene or the

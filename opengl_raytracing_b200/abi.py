@@ -37,9 +37,10 @@ EXPORTED_SYMBOLS = [
     "rt_ipc_open", "rt_ipc_close", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
     "rt_debug_light_grids", "rt_tune", "rt_get_tuning", "rt_set_tuning", "rt_set_autotune",
 ]
-KERNEL_AUTO, KERNEL_MEGAKERNEL, KERNEL_WAVEFRONT, KERNEL_LITERAL = -1, 0, 1, 2
+KERNEL_AUTO, KERNEL_MEGAKERNEL, KERNEL_WAVEFRONT, KERNEL_LITERAL, KERNEL_REGROUP = -1, 0, 1, 2, 3
 TUNING_DEFAULT, TUNING_TRIALS, TUNING_CHOSEN, TUNING_PINNED = range(4)
-KERNEL_NAMES = {-1: "auto", 0: "megakernel", 1: "wavefront", 2: "literal"}
+KERNEL_NAMES = {-1: "auto", 0: "megakernel", 1: "wavefront", 2: "literal", 3: "regroup"}
+KERNEL_IDS = {v: k for k, v in KERNEL_NAMES.items()}
 POST_EXPORTED_SYMBOLS = [                   # include/rt_post.h
     "rt_generate_aabbs", "rt_generate_aabbs_device", "rt_decode_rgbe", "rt_equirect_to_cubemap",
     "rt_bloom_extract", "rt_gaussian_blur", "rt_bloom_combine", "rt_taa_resolve", "rt_post_chain", "rt_post_launch_count",

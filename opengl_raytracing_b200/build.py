@@ -25,7 +25,7 @@ UNITS = [  # (source, extra flags)
     ("rt_peak.cu", []),
     ("rt_multi.cu", []),
 ]
-HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_wavefront.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
+HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_wavefront.cuh", "rt_regroup.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
            os.path.join("..", "..", "include", "rt_post.h"), os.path.join("..", "..", "include", "rt_frame.h"),
            os.path.join("..", "..", "include", "rt_multi.h")]
 

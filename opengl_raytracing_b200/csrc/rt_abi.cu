@@ -76,11 +76,15 @@ struct rt_context {
   bool pinned = false; Variant pin = {0, 0, 0};
   int last_kernel = -1, last_dense = 0, last_coherent = 0;
   uint64_t tune_clock = 0;
+  int regroup_override = -1;    // RT_PK_REGROUP=0 removes the regrouping megakernel from the variants, 1 pins it
   int wavefront_override = -1;  // RT_PK_WAVEFRONT=0 removes the wavefront pipeline from the variants, 1 pins it
   void* wf_state = nullptr;     // wavefront queues (rt_wavefront.cuh), sized on first use
   size_t wf_bytes = 0;
   cudaEvent_t wf_done = nullptr;
-  size_t wf_chunk_pixels = (size_t)1 << 21;   // RT_WF_CHUNK: pixels per wavefront chunk (queue memory ~ 300 B per pixel)
+  // RT_WF_CHUNK: pixels per wavefront chunk (queue memory ~ 300 B per pixel: 2.6 GB at the default, a whole 4K frame).
+  // Measured on B200 (C3 4K / C5 8K, ms): 0.5 M 18.3 / 13.3, 1 M 15.5 / 10.4, 2 M 14.4 / 8.9, 4 M 13.9 / 8.1, 9 M 13.4 / 7.7 —
+  // every chunk pays the ramp-up and tail of 2 D + 1 launches.
+  size_t wf_chunk_pixels = (size_t)1 << 23;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t band_done[16] = {};
   cudaStream_t stream = nullptr;
@@ -570,6 +574,7 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if (const char* e3 = getenv("RT_PK_DENSE")) c->dense_override = atoi(e3);
   if (const char* e4 = getenv("RT_PK_FAN")) c->fan_override = atoi(e4);
   if (const char* e5 = getenv("RT_PK_GRID")) c->grid_override = atoi(e5);
+  if (const char* e9 = getenv("RT_PK_REGROUP")) c->regroup_override = atoi(e9);
   if (const char* e6 = getenv("RT_PK_WAVEFRONT")) c->wavefront_override = atoi(e6);
   if (const char* e8 = getenv("RT_WF_CHUNK")) c->wf_chunk_pixels = (size_t)atoll(e8) > 0 ? (size_t)atoll(e8) : c->wf_chunk_pixels;
   if (const char* e7 = getenv("RT_AUTOTUNE")) c->autotune = atoi(e7) != 0;
@@ -815,7 +820,12 @@ static rt_status plan_launch(rt_context* c, const rt_frame_params* p, LaunchPlan
           L.v[L.nv++] = {RT_KERNEL_MEGAKERNEL, dense, c->coherent_override >= 0 ? c->coherent_override : coh};
         }
     }
-    if (rt::wavefront_supported(kp) && c->wavefront_override != 0) {
+    if (sc.num_lights <= rt::regroup_max_lights() && c->regroup_override != 0 &&
+        rt::regroup_smem_bytes((int)c->pk_float4s, sc.num_lights) <= (size_t)c->max_smem_optin - 1024) {
+      if (c->regroup_override == 1) L.nv = 0;              // RT_PK_REGROUP=1 pins it
+      L.v[L.nv++] = {RT_KERNEL_REGROUP, 0, 0};
+    }
+    if (rt::wavefront_supported(kp) && c->wavefront_override != 0 && c->regroup_override != 1) {
       if (c->wavefront_override == 1) L.nv = 0;            // RT_PK_WAVEFRONT=1 pins it
       L.v[L.nv++] = {RT_KERNEL_WAVEFRONT, 0, 0};
     }
@@ -918,16 +928,21 @@ static rt_status launch_variant(rt_context* c, LaunchPlan& L, rt_context::Varian
                                 int32_t* d_object_id, cudaStream_t stream) {
   rt::KernelParams& kp = L.kp;
   kp.color = (float4*)d_color; kp.position = (float4*)d_position; kp.normal = d_normal; kp.object_id = d_object_id;
+  kp.sc.pk_dense = v.dense; kp.sc.pk_coherent = v.coherent;
+  if (L.use_packet && v.kernel == RT_KERNEL_WAVEFRONT) {   // its launches take their work from the queue counters, not from a slot
+    rt_status st = wavefront_render(c, L, stream);
+    if (st != RT_OK) return st;
+    c->last_kernel = v.kernel; c->last_dense = 0; c->last_coherent = 0;
+    return RT_OK;
+  }
   rt_context::CounterSlot& slot = c->slots[c->next_slot];
   if (slot.used) RT_CUDA(c, cudaStreamWaitEvent(stream, slot.done, 0));   // a no-op when the previous user ran on this stream
   kp.tile_counter = c->d_tile_counter + 32 * c->next_slot; kp.tile_base = slot.base;
-  kp.sc.pk_dense = v.dense; kp.sc.pk_coherent = v.coherent;
   unsigned advance = 0;
   cudaError_t e;
-  if (L.use_packet && v.kernel == RT_KERNEL_WAVEFRONT) {
-    rt_status st = wavefront_render(c, L, stream);
-    if (st != RT_OK) return st;
-    e = cudaSuccess;
+  if (L.use_packet && v.kernel == RT_KERNEL_REGROUP) {
+    e = L.par ? rt::launch_regroup_parity(kp, c->sm_count, stream, &advance) : rt::launch_regroup_fast(kp, c->sm_count, stream, &advance);
+    c->launches += 1;
   } else if (L.use_packet) {
     e = L.par ? rt::launch_packet_parity(kp, c->sm_count, stream, &advance) : rt::launch_packet_fast(kp, c->sm_count, stream, &advance);
     c->launches += 1;
@@ -1014,9 +1029,16 @@ rt_status rt_tune(rt_context* c, const rt_frame_params* p, rt_tuning* out) {
   cudaEvent_t e0, e1;
   RT_CUDA(c, cudaEventCreate(&e0)); RT_CUDA(c, cudaEventCreate(&e1));
   const bool acc = (p->flags & RT_FLAG_ACCUMULATE) != 0u;
+  // Each timed launch is enqueued BEHIND an untimed launch of the same variant, without synchronising in between: the
+  // device is still busy while the host enqueues (e0, launch, e1), so the events bracket device time only — timing a
+  // launch into an idle device would add the host's launch path (tens of microseconds, several launches for the
+  // wavefront pipeline) to a 0.1 - 0.4 ms frame.
   for (int i = 0; i < t->nv && st == RT_OK; ++i) {
     float best = 0.0f;
-    for (int k = 0; k <= rt_context::kTuneTrials && st == RT_OK; ++k) {           // k = 0: untimed
+    for (int k = 0; k < rt_context::kTuneTrials && st == RT_OK; ++k) {
+      if (acc) cudaMemsetAsync(c->o_color, 0, (size_t)p->width * p->height * sizeof(float4), c->stream);
+      st = launch_variant(c, L, t->v[i], (float*)c->o_color, (float*)c->o_position, c->o_normal, nullptr, c->stream);
+      if (st != RT_OK) break;
       if (acc) cudaMemsetAsync(c->o_color, 0, (size_t)p->width * p->height * sizeof(float4), c->stream);
       cudaEventRecord(e0, c->stream);
       st = launch_variant(c, L, t->v[i], (float*)c->o_color, (float*)c->o_position, c->o_normal, nullptr, c->stream);
@@ -1024,7 +1046,7 @@ rt_status rt_tune(rt_context* c, const rt_frame_params* p, rt_tuning* out) {
       if (st != RT_OK) break;
       float ms = 0.0f;
       if (cudaEventSynchronize(e1) != cudaSuccess || cudaEventElapsedTime(&ms, e0, e1) != cudaSuccess) { st = cuda_fail(c, cudaGetLastError(), "rt_tune"); break; }
-      if (k == 1 || (k > 1 && ms < best)) best = ms;
+      if (k == 0 || ms < best) best = ms;
     }
     t->ms[i] = best;
   }
@@ -1062,7 +1084,7 @@ rt_status rt_get_tuning(rt_context* c, const rt_frame_params* p, rt_tuning* out)
 rt_status rt_set_tuning(rt_context* c, const rt_tuning* tuning) {
   if (!c) return RT_ERR_INVALID_ARG;
   if (!tuning) { c->pinned = false; return RT_OK; }
-  if (tuning->kernel > RT_KERNEL_WAVEFRONT || tuning->registers > 1 || tuning->phase_level > 3)
+  if (tuning->kernel > RT_KERNEL_REGROUP || tuning->kernel == RT_KERNEL_LITERAL || tuning->registers > 1 || tuning->phase_level > 3)
     return fail(c, RT_ERR_INVALID_ARG, "rt_set_tuning: kernel / registers / phase_level out of range");
   c->pinned = true;
   c->pin = {tuning->kernel, tuning->registers, tuning->phase_level};

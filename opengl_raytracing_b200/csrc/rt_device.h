@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
 #include <string>
 #include "../../include/rt_abi.h"
 
@@ -79,6 +80,39 @@ struct KernelParams {
 };
 
 size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights);
+
+// Resident CTAs per SM of `kernel` at `threads` threads and `smem` bytes of dynamic shared memory, with the
+// kernel's dynamic shared-memory limit raised to `smem` — cached per (kernel, device, smem): the two runtime
+// calls behind it cost tens of microseconds of host time, which is a visible share of a 0.1 - 0.4 ms frame and of
+// every launch of the wavefront pipeline. One cache per kernel instantiation (function-local static of the template).
+template <typename K>
+inline cudaError_t cached_occupancy(K kernel, int threads, size_t smem, int* per_sm) {
+  struct Entry { int device; size_t smem; int per_sm; };
+  static Entry cache[8];
+  static int used = 0;
+  static std::mutex lock;                      // contexts of different devices may launch from different threads
+  std::lock_guard<std::mutex> guard(lock);
+  int device = 0;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess) return e;
+  for (int i = 0; i < used; ++i)
+    if (cache[i].device == device && cache[i].smem == smem) { *per_sm = cache[i].per_sm; return cudaSuccess; }
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int n = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem);
+  if (e != cudaSuccess) return e;
+  if (n < 1) n = 1;
+  // the attribute is a per-device maximum: a cached smaller size stays valid only while no larger one replaced it,
+  // so a new size evicts every entry of this device (scenes change rarely; sizes alternate almost never)
+  int w = 0;
+  for (int i = 0; i < used; ++i) if (cache[i].device != device) cache[w++] = cache[i];
+  used = w;
+  if (used == 8) used = 7;
+  cache[used++] = Entry{device, smem, n};
+  *per_sm = n;
+  return cudaSuccess;
+}
 // ---- wavefront pipeline (rt_wavefront.cuh): the same pass as three kinds of launches over compacted
 // queues in global memory instead of one persistent megakernel. Per sample and per chunk of tile rows:
 //   bounce(0) shadow(0) bounce(1) shadow(1) ... bounce(D-1) shadow(D-1) bounce(D)
@@ -109,6 +143,11 @@ struct WfParams {
 };
 bool wavefront_supported(const KernelParams& kp);
 size_t packet_smem_bytes(int pk_float4s);   // dynamic shared memory of the packet / wavefront kernels for a blob of that size
+// the persistent megakernel with in-CTA ray regrouping (rt_regroup.cuh)
+size_t regroup_smem_bytes(int pk_float4s, int num_lights);
+int regroup_max_lights();
+cudaError_t launch_regroup_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance);
+cudaError_t launch_regroup_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance);
 cudaError_t launch_wf_bounce_fast(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
 cudaError_t launch_wf_bounce_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
 cudaError_t launch_wf_shadow_fast(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);

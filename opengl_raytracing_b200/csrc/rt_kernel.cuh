@@ -488,12 +488,9 @@ inline cudaError_t launch_render(const KernelParams& kp, int sm_count, cudaStrea
   const bool count = (kp.fp.flags & RT_FLAG_COUNTERS) != 0u;
   const size_t smem = kp.sc.scene_in_smem ? scene_smem_bytes(kp.sc.num_objects, kp.sc.num_planes, kp.sc.num_lights) : 0;
   auto kern = count ? rt_render_kernel<true> : rt_render_kernel<false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem);
+  cudaError_t e = count ? cached_occupancy(rt_render_kernel<true>, kThreads, smem, &per_sm) : cached_occupancy(rt_render_kernel<false>, kThreads, smem, &per_sm);
   if (e != cudaSuccess) return e;
-  if (per_sm < 1) per_sm = 1;
   const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
   unsigned ctas = (unsigned)(sm_count * per_sm);
   const unsigned needed = (num_tiles + kWarpsPerCta - 1) / kWarpsPerCta;

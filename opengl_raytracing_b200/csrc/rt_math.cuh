@@ -173,7 +173,15 @@ __device__ __forceinline__ f3 fetch_sky(const Textures& tx, f3 r) {
 
 // random (glsl:273-275). The sine is evaluated in FP64 and rounded: it decides Russian
 // roulette, and 1 ulp of sinf moves fract(sin*43758.5) by 2.6e-3.
-__device__ __forceinline__ float random2(float sx, float sy) {
+#ifndef RT_INLINE_RANDOM
+#define RT_INLINE_RANDOM 1
+#endif
+#if RT_INLINE_RANDOM
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+float random2(float sx, float sy) {
   const float arg = sx * 12.9898f + sy * 78.233f;
   return fract_((float)sin((double)arg) * 43758.5453123f);
 }
@@ -251,7 +259,15 @@ __device__ __forceinline__ f3 compute_pbr(const Mat& mat, f3 N, f3 V, f3 L, f3 H
 
 // calculateRefraction (glsl:256-270), refract() per GLSL 4.30 §8.5. The TIR decision and the
 // new direction feed the next intersection -> IEEE forms in both variants.
-__device__ __forceinline__ f3 refraction_dir(f3 d, f3 N, float ior) {
+#ifndef RT_INLINE_REFRACT
+#define RT_INLINE_REFRACT 1
+#endif
+#if RT_INLINE_REFRACT
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+f3 refraction_dir(f3 d, f3 N, float ior) {
   const bool entering = dot3(d, N) < 0.0f;
   const float eta = entering ? rcp_ieee(ior) : ior;
   const f3 n = entering ? N : -N;

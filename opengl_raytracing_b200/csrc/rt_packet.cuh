@@ -1095,12 +1095,9 @@ inline cudaError_t upload_probe_order(const float* halton3, const int* order16) 
 template <bool BIG, bool BANDS, int MINB, bool FAN>
 inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
   const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
-  cudaError_t e = cudaFuncSetAttribute(rt_packet_kernel<BIG, BANDS, MINB, FAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rt_packet_kernel<BIG, BANDS, MINB, FAN>, kThreads, smem);
+  cudaError_t e = cached_occupancy(rt_packet_kernel<BIG, BANDS, MINB, FAN>, kThreads, smem, &per_sm);
   if (e != cudaSuccess) return e;
-  if (per_sm < 1) per_sm = 1;
   const unsigned num_tiles = kp.tiles_x * kp.tiles_y;
   unsigned ctas = (unsigned)(sm_count * per_sm);
   const unsigned needed = (num_tiles + kWarpsPerCta - 1) / kWarpsPerCta;

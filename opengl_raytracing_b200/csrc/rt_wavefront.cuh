@@ -359,12 +359,9 @@ wf_shadow_kernel(const __grid_constant__ KernelParams kp, const __grid_constant_
 template <typename K>
 inline cudaError_t wf_launch(K kernel, const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream) {
   const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, smem);
+  cudaError_t e = cached_occupancy(kernel, kThreads, smem, &per_sm);
   if (e != cudaSuccess) return e;
-  if (per_sm < 1) per_sm = 1;
   kernel<<<(unsigned)(sm_count * per_sm), kThreads, smem, stream>>>(kp, wp);
   return cudaGetLastError();
 }

@@ -277,11 +277,11 @@ def test_fast_packet_kernel_stays_close_to_fast_literal_kernel(rt_ctx):
 
 def test_config4_multisample_mean(rt_ctx, port_oracle):
     """C4 at reduced size: exact-sequence test (same Hammersley indices, sequential FP32 sum)."""
-    w = synthetic.config(4, 128, 72)
-    w.num_samples = 8
+    w = synthetic.config(4, 160, 90)
+    w.num_samples = 16
     o = port_oracle.render(w, "port", margins=True)
     k = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32)
-    st = record("C4 128x72 x 8 spp fast vs port", compare(k, o))
+    st = record("C4 160x90 x 16 spp fast vs port", compare(k, o))
     assert_parity(st, strict_geom=False)
 
 

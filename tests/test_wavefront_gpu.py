@@ -1,6 +1,8 @@
-"""The wavefront variant (csrc/rt_wavefront.cuh: bounce / shadow-job launches over ballot-compacted ray
-queues) against the persistent megakernel, through the C ABI (rt_set_tuning pins the variant). Both run the
-same per-pixel arithmetic — only which lane runs it differs — so every image must agree BIT FOR BIT, in both
+"""The two ray-regrouping variants — the wavefront pipeline (csrc/rt_wavefront.cuh: bounce / shadow-job launches
+over ballot-compacted ray queues in HBM) and the regrouping megakernel (csrc/rt_regroup.cuh: the same rounds
+inside a persistent CTA, queues in shared memory) — against the plain persistent megakernel, through the C ABI
+(rt_set_tuning pins the variant). All run the same per-pixel arithmetic — only which lane runs it differs — so
+every image must agree BIT FOR BIT, in both
 math builds: the five BASELINE configs, multi-sample sums, row windows and interleaved bands, ragged sizes,
 the edge-case scenes, several chunkings of the frame, and the explicit tuning entry points."""
 import os
@@ -21,18 +23,32 @@ ZERO = {"color": 0, "position": 0, "normal": 0, "object_id": 0}
 
 
 def _bits_equal(a: dict, b: dict) -> dict:
-    return {k: int((a[k].view(np.uint32) != b[k].view(np.uint32)).sum()) if a[k].dtype == np.float32
-            else int((a[k] != b[k]).sum()) for k in ("color", "position", "normal", "object_id")}
+    d = {k: int((a[k].view(np.uint32) != b[k].view(np.uint32)).sum()) if a[k].dtype == np.float32
+         else int((a[k] != b[k]).sum()) for k in ("color", "position", "normal", "object_id")}
+    if hasattr(b, "other"):                    # the regrouping megakernel's image rides along with the wavefront's
+        for k, v in _bits_equal(a, b.other).items():
+            d[k] += v
+    return d
+
+
+class _Many(dict):
+    pass
 
 
 def _both(ctx, w, flags, params=None, bind=True):
+    """Renders with the megakernel, the wavefront pipeline and the regrouping megakernel; returns (megakernel image,
+    images of the other two merged for _bits_equal: a differing element in EITHER counts)."""
     ctx.set_tuning(abi.KERNEL_MEGAKERNEL)
     a = render_workload(ctx, w, flags=flags, params=params, bind=bind)
     assert ctx.get_tuning()["kernel"] == "megakernel"
-    ctx.set_tuning(abi.KERNEL_WAVEFRONT)
-    b = render_workload(ctx, w, flags=flags, params=params, bind=False)
-    assert ctx.get_tuning()["kernel"] == "wavefront"
+    others = []
+    for kern, name in ((abi.KERNEL_WAVEFRONT, "wavefront"), (abi.KERNEL_REGROUP, "regroup")):
+        ctx.set_tuning(kern)
+        others.append(render_workload(ctx, w, flags=flags, params=params, bind=False))
+        assert ctx.get_tuning()["kernel"] == name
     ctx.set_tuning(None)
+    b = _Many(others[0])
+    b.other = others[1]
     return a, b
 
 
@@ -110,7 +126,7 @@ def test_wavefront_row_windows_bands_and_sample_modes(rt_ctx):
     H, W = w.height, w.width
     st = torch.cuda.current_stream().cuda_stream
     outs = {}
-    for kern in (abi.KERNEL_MEGAKERNEL, abi.KERNEL_WAVEFRONT):
+    for kern in (abi.KERNEL_MEGAKERNEL, abi.KERNEL_WAVEFRONT, abi.KERNEL_REGROUP):
         rt_ctx.set_tuning(kern)
         color = torch.full((H, W, 4), 0.25, device="cuda"); pos = torch.zeros(H, W, 4, device="cuda")
         nrm = torch.zeros(H, W, 4, dtype=torch.float16, device="cuda"); oid = torch.full((H, W), -9, dtype=torch.int32, device="cuda")
@@ -126,8 +142,9 @@ def test_wavefront_row_windows_bands_and_sample_modes(rt_ctx):
         torch.cuda.synchronize()
         outs[kern] = [t.cpu().numpy() for t in (color, pos, nrm.float(), oid, acc, sums)]
     rt_ctx.set_tuning(None)
-    for x, y in zip(outs[abi.KERNEL_MEGAKERNEL], outs[abi.KERNEL_WAVEFRONT]):
-        assert np.array_equal(x, y, equal_nan=True)
+    for other in (abi.KERNEL_WAVEFRONT, abi.KERNEL_REGROUP):
+        for x, y in zip(outs[abi.KERNEL_MEGAKERNEL], outs[other]):
+            assert np.array_equal(x, y, equal_nan=True), other
     assert (outs[abi.KERNEL_WAVEFRONT][3] >= -1).all()          # every pixel of the frame was written exactly by its window
 
 
@@ -147,7 +164,7 @@ def test_overlapping_launches_on_two_streams(rt_ctx):
     bind_workload(rt_ctx, w)
     ref = render_workload(rt_ctx, w, bind=False)
     s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
-    for kern in (abi.KERNEL_MEGAKERNEL, abi.KERNEL_WAVEFRONT):
+    for kern in (abi.KERNEL_MEGAKERNEL, abi.KERNEL_WAVEFRONT, abi.KERNEL_REGROUP):
         rt_ctx.set_tuning(kern)
         bufs = [torch.zeros(w.height, w.width, 4, device="cuda") for _ in range(6)]
         torch.cuda.synchronize()

@@ -1,5 +1,5 @@
 """Dev helper (GPU box, under ncu): renders one BASELINE config with a pinned variant.
-usage: python tools/render_once.py CONFIG megakernel|wavefront [frames] [registers] [phase_level] [WxH]"""
+usage: python tools/render_once.py CONFIG megakernel|wavefront|regroup [frames] [registers] [phase_level] [WxH]"""
 import sys
 sys.path.insert(0, ".")
 import torch
@@ -17,7 +17,7 @@ if n == 4:
 ctx = RtContext(0)
 bind_workload(ctx, w)
 ctx.set_autotune(False)
-ctx.set_tuning(abi.KERNEL_WAVEFRONT if kern == "wavefront" else abi.KERNEL_MEGAKERNEL, regs, phase)
+ctx.set_tuning(abi.KERNEL_IDS[kern], regs, phase)
 H, W = w.height, w.width
 c = torch.zeros(H, W, 4, device="cuda"); p = torch.zeros(H, W, 4, device="cuda"); nn = torch.zeros(H, W, 4, dtype=torch.float16, device="cuda")
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
