@@ -87,8 +87,9 @@ size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights);
 // every launch of the wavefront pipeline. One cache per kernel instantiation (function-local static of the template).
 template <typename K>
 inline cudaError_t cached_occupancy(K kernel, int threads, size_t smem, int* per_sm) {
-  struct Entry { int device; size_t smem; int per_sm; };
-  static Entry cache[8];
+  // (K is the function-pointer TYPE, shared by every kernel of the same signature: the kernel's address is part of the key)
+  struct Entry { const void* fn; int device; size_t smem; int per_sm; };
+  static Entry cache[32];
   static int used = 0;
   static std::mutex lock;                      // contexts of different devices may launch from different threads
   std::lock_guard<std::mutex> guard(lock);
@@ -96,7 +97,7 @@ inline cudaError_t cached_occupancy(K kernel, int threads, size_t smem, int* per
   cudaError_t e = cudaGetDevice(&device);
   if (e != cudaSuccess) return e;
   for (int i = 0; i < used; ++i)
-    if (cache[i].device == device && cache[i].smem == smem) { *per_sm = cache[i].per_sm; return cudaSuccess; }
+    if (cache[i].fn == (const void*)kernel && cache[i].device == device && cache[i].smem == smem) { *per_sm = cache[i].per_sm; return cudaSuccess; }
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int n = 0;
@@ -106,10 +107,10 @@ inline cudaError_t cached_occupancy(K kernel, int threads, size_t smem, int* per
   // the attribute is a per-device maximum: a cached smaller size stays valid only while no larger one replaced it,
   // so a new size evicts every entry of this device (scenes change rarely; sizes alternate almost never)
   int w = 0;
-  for (int i = 0; i < used; ++i) if (cache[i].device != device) cache[w++] = cache[i];
+  for (int i = 0; i < used; ++i) if (cache[i].device != device || cache[i].fn != (const void*)kernel) cache[w++] = cache[i];
   used = w;
-  if (used == 8) used = 7;
-  cache[used++] = Entry{device, smem, n};
+  if (used == 32) used = 31;
+  cache[used++] = Entry{(const void*)kernel, device, smem, n};
   *per_sm = n;
   return cudaSuccess;
 }
