@@ -226,6 +226,22 @@ rt_status rt_render(rt_context* ctx, const rt_frame_params* params,
                     float* d_color_rgba32f, float* d_position_rgba32f,
                     void* d_normal, int32_t* d_object_id, void* cuda_stream);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same arguments, same images as rt_render
+ * (bit for bit), but the call allocates NOTHING: it runs the wavefront pipeline with its ray queues in a file-scope
+ * `static __device__` array of RT_STATIC_SCRATCH_BYTES (64 MiB) that every GPU loading the library holds until the process
+ * exits, cutting the frame into chunks of tile rows that fit (so large frames take more, smaller launches than rt_render).
+ * Limits, rejected with RT_ERR_INVALID_ARG and a message in rt_last_error: num_samples must be 1; no COUNTERS /
+ * LITERAL_KERNEL flags; the scene must be one the wavefront pipeline takes (staged in shared memory, <= 32 lights,
+ * depth <= 16); one tile row of queues must fit: (ceil(width / 8) * 32) * (160 + 36 * max(lights, 1)) bytes <= 64 MiB - 4 608
+ * (width <= 62592 at 3 lights, 12784 at 32). The array is SHARED by every call on the device and keeps the previous call's
+ * contents (the call clears the queue counters itself, nothing else needs to start at zero): two calls that overlap on the
+ * GPU — different streams, different contexts of one device, different threads — race; order them on one stream. */
+#define RT_STATIC_SCRATCH_BYTES (64u << 20)
+rt_status rt_render_static(rt_context* ctx, const rt_frame_params* params,
+                           float* d_color_rgba32f, float* d_position_rgba32f,
+                           void* d_normal, int32_t* d_object_id, void* cuda_stream);
+
 /* One whole reference frame through HOST buffers, as ForwardShadingPipline::Render does
  * it (SSBO upload every frame, dispatch, read-back): scene H2D + render + D2H of the
  * rendered rows into pinned or pageable host buffers. objects/lights may be NULL to

@@ -20,6 +20,13 @@ size_t scene_smem_bytes(int num_objects, int num_planes, int num_lights) {
 cudaError_t measure_fp32_peak(int sm_count, cudaStream_t stream, double* tflops, double* ms);   // rt_peak.cu
 }  // namespace rt
 
+// ---- rt_render_static: the wavefront queues in a file-scope device array instead of a cudaMalloc'ed buffer, for callers that
+// may not allocate (include/rt_abi.h). Every GPU that loads the library holds these 64 MiB until the process exits. In HOST
+// code the name below is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress (rt_create, once
+// per context, with the context's device current) and is what the kernels are given.
+constexpr size_t kStaticScratchBytes = (size_t)64 << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
 struct rt_context {
   int device = 0;
   int sm_count = 0;
@@ -81,6 +88,8 @@ struct rt_context {
   void* wf_state = nullptr;     // wavefront queues (rt_wavefront.cuh), sized on first use
   size_t wf_bytes = 0;
   cudaEvent_t wf_done = nullptr;
+  void* static_scratch = nullptr;          // device address of g_static_scratch on this context's device (rt_create)
+  std::string static_scratch_err;          // why it could not be resolved
   // RT_WF_CHUNK: pixels per wavefront chunk (queue memory ~ 300 B per pixel: 2.6 GB at the default, a whole 4K frame).
   // Measured on B200 (C3 4K / C5 8K, ms): 0.5 M 18.3 / 13.3, 1 M 15.5 / 10.4, 2 M 14.4 / 8.9, 4 M 13.9 / 8.1, 9 M 13.4 / 7.7 —
   // every chunk pays the ramp-up and tail of 2 D + 1 launches.
@@ -559,6 +568,12 @@ rt_status rt_create(rt_context** out, int cuda_device) {
   if ((e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * RT_CNT_COUNT)) != cudaSuccess) return bail(e);
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e);
   if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e);
+  {                                                      // set-up of rt_render_static: resolve the scratch array on THIS device
+    void* sp = nullptr;
+    const cudaError_t es = cudaGetSymbolAddress(&sp, g_static_scratch);
+    if (es == cudaSuccess) c->static_scratch = sp;
+    else { c->static_scratch_err = cudaGetErrorString(es); cudaGetLastError(); }
+  }
   for (int i = 0; i < 16; ++i)
     if ((e = cudaEventCreateWithFlags(&c->band_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e);
   if ((e = cudaEventCreateWithFlags(&c->stage_done, cudaEventDisableTiming)) != cudaSuccess) return bail(e);
@@ -1094,6 +1109,74 @@ rt_status rt_set_tuning(rt_context* c, const rt_tuning* tuning) {
 rt_status rt_set_autotune(rt_context* c, int on) {
   if (!c) return RT_ERR_INVALID_ARG;
   c->autotune = on != 0;
+  return RT_OK;
+}
+
+// The wavefront pipeline (rt_wavefront.cuh) with its ray queues in g_static_scratch. Calls no cudaMalloc / cudaFree and no
+// allocating routine: the array's address was resolved in rt_create, the launch configurations come from the per-kernel
+// cache, and the frame is cut into chunks of tile rows that fit the array. The queue counters are the only part of the
+// scratch that must start at zero: cleared per chunk on the caller's stream. Everything else is written before it is read.
+rt_status rt_render_static(rt_context* c, const rt_frame_params* p, float* d_color, float* d_position, void* d_normal,
+                           int32_t* d_object_id, void* cuda_stream) {
+  if (!c || !p) return RT_ERR_INVALID_ARG;
+  if (!c->static_scratch) return fail(c, RT_ERR_CUDA, "rt_render_static: cudaGetSymbolAddress of the scratch array failed at rt_create: " + c->static_scratch_err);
+  LaunchPlan L;
+  rt_status st = plan_launch(c, p, L);
+  if (st != RT_OK || L.skip) return st;
+  rt::KernelParams& kp = L.kp;
+  const int nsamp = p->num_samples > 0 ? p->num_samples : 1;
+  if (nsamp != 1) return fail(c, RT_ERR_INVALID_ARG, "rt_render_static: num_samples must be 1 (a multi-sample frame needs a full-frame accumulator; use rt_render)");
+  if (p->flags & (RT_FLAG_COUNTERS | RT_FLAG_LITERAL_KERNEL)) return fail(c, RT_ERR_INVALID_ARG, "rt_render_static: COUNTERS / LITERAL_KERNEL are not supported");
+  if (!L.use_packet || !rt::wavefront_supported(kp))
+    return fail(c, RT_ERR_INVALID_ARG, "rt_render_static: the scene must be fully staged in shared memory and have at most 32 lights, depth <= 16 (use rt_render)");
+  RT_CUDA(c, cudaSetDevice(c->device));
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  const int nl = kp.sc.num_lights, D = kp.fp.max_ray_depth, nlp = nl > 0 ? nl : 1;
+  const size_t counter_bytes = (rt::kWfCounters * sizeof(unsigned) + 255) / 256 * 256;
+  const size_t slot_bytes = (size_t)(2 * 3 + 2 * 2 + 2 * nlp) * sizeof(float4) + (size_t)nlp * sizeof(unsigned);
+  const size_t per_row = (size_t)kp.tiles_x * 32u;              // queue slots of one tile row (4 image rows)
+  size_t rows_per_chunk = (kStaticScratchBytes - counter_bytes) / (per_row * slot_bytes);
+  if (rows_per_chunk < 1) {
+    char msg[256];
+    snprintf(msg, sizeof(msg), "rt_render_static: one tile row of width %d with %d lights needs %zu bytes of queues, the static scratch holds %zu "
+             "(maximum width at this light count: %zu pixels)", p->width, nl, per_row * slot_bytes + counter_bytes, kStaticScratchBytes,
+             (kStaticScratchBytes - counter_bytes) / (slot_bytes * 32u) * 8u);
+    return fail(c, RT_ERR_INVALID_ARG, msg);
+  }
+  if (rows_per_chunk > kp.tiles_y) rows_per_chunk = kp.tiles_y;
+  const size_t cap = rows_per_chunk * per_row;
+  kp.color = (float4*)d_color; kp.position = (float4*)d_position; kp.normal = d_normal; kp.object_id = d_object_id;
+  kp.sc.pk_dense = 0; kp.sc.pk_coherent = 0;
+  rt::WfParams wp;
+  std::memset(&wp, 0, sizeof(wp));
+  unsigned char* base = (unsigned char*)c->static_scratch;
+  wp.counters = (unsigned*)base;
+  float4* f = (float4*)(base + counter_bytes);
+  wp.path[0] = f; f += 3 * cap; wp.path[1] = f; f += 3 * cap;
+  wp.hit[0] = f; f += 2 * cap; wp.hit[1] = f; f += 2 * cap;
+  wp.brdf[0] = f; f += (size_t)nlp * cap; wp.brdf[1] = f; f += (size_t)nlp * cap;
+  wp.jobq = (unsigned*)f;
+  wp.acc = nullptr;
+  wp.cap = (unsigned)cap;
+  wp.sample = 0;
+  nvtxRangePushA("rt_render_static");
+  struct Pop { ~Pop() { nvtxRangePop(); } } pop;
+  for (unsigned row0 = 0; row0 < kp.tiles_y; row0 += (unsigned)rows_per_chunk) {
+    wp.tile_row0 = row0;
+    wp.tile_rows = kp.tiles_y - row0 < (unsigned)rows_per_chunk ? kp.tiles_y - row0 : (unsigned)rows_per_chunk;
+    RT_CUDA(c, cudaMemsetAsync(wp.counters, 0, rt::kWfCounters * sizeof(unsigned), stream));
+    for (int d = 0; d <= D; ++d) {
+      wp.depth = d;
+      cudaError_t e = L.par ? rt::launch_wf_bounce_parity(kp, wp, c->sm_count, stream) : rt::launch_wf_bounce_fast(kp, wp, c->sm_count, stream);
+      if (e != cudaSuccess) return cuda_fail(c, e, "rt_render_static: bounce launch");
+      c->launches += 1;
+      if (d == D || nl == 0) continue;
+      e = L.par ? rt::launch_wf_shadow_parity(kp, wp, c->sm_count, stream) : rt::launch_wf_shadow_fast(kp, wp, c->sm_count, stream);
+      if (e != cudaSuccess) return cuda_fail(c, e, "rt_render_static: shadow launch");
+      c->launches += 1;
+    }
+  }
+  c->last_kernel = RT_KERNEL_WAVEFRONT; c->last_dense = 0; c->last_coherent = 0;
   return RT_OK;
 }
 

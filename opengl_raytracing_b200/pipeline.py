@@ -95,6 +95,12 @@ class RtContext:
         self._check(self.lib.rt_render(self.handle, C.byref(params), _ptr(color), _ptr(position), _ptr(normal),
                                        _ptr(object_id), C.c_void_p(stream)))
 
+    # rt_render_static: rt_render without any allocation (wavefront queues in a static device array, include/rt_abi.h)
+    def render_static(self, params: abi.FrameParams, color=None, position=None, normal=None, object_id=None,
+                      stream: int = 0) -> None:
+        self._check(self.lib.rt_render_static(self.handle, C.byref(params), _ptr(color), _ptr(position), _ptr(normal),
+                                              _ptr(object_id), C.c_void_p(stream)))
+
     def render_host(self, params: abi.FrameParams, objects, lights, color, position, normal, object_id=None) -> None:
         n = 0 if objects is None else len(objects)
         m = 0 if lights is None else len(lights)
