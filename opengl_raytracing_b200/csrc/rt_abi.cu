@@ -1044,6 +1044,19 @@ rt_status rt_tune(rt_context* c, const rt_frame_params* p, rt_tuning* out) {
   cudaEvent_t e0, e1;
   RT_CUDA(c, cudaEventCreate(&e0)); RT_CUDA(c, cudaEventCreate(&e1));
   const bool acc = (p->flags & RT_FLAG_ACCUMULATE) != 0u;
+  // Warm-up first: a device that has been idle runs its first milliseconds below its boost clock (B200: a 0.36 ms frame
+  // reads 0.41 ms when it is timed 10 ms after the context was created), which would penalise whichever variant is timed
+  // first. >= 60 ms of default-variant launches, checked every 8 launches.
+  {
+    cudaEventRecord(e0, c->stream);
+    for (int round = 0; round < 4096 && st == RT_OK; ++round) {
+      for (int k = 0; k < 8 && st == RT_OK; ++k)
+        st = launch_variant(c, L, t->v[0], (float*)c->o_color, (float*)c->o_position, c->o_normal, nullptr, c->stream);
+      cudaEventRecord(e1, c->stream);
+      float ms = 0.0f;
+      if (cudaEventSynchronize(e1) != cudaSuccess || cudaEventElapsedTime(&ms, e0, e1) != cudaSuccess || ms >= 60.0f) break;
+    }
+  }
   // Each timed launch is enqueued BEHIND an untimed launch of the same variant, without synchronising in between: the
   // device is still busy while the host enqueues (e0, launch, e1), so the events bracket device time only — timing a
   // launch into an idle device would add the host's launch path (tens of microseconds, several launches for the

@@ -233,12 +233,61 @@ __global__ void __launch_bounds__(256) blur_kernel(const uint2* __restrict__ in,
 //      CLAMP_TO_EDGE taps then simply read their neighbours), row stride 73 texels (odd: the H pass
 //      walks rows with one lane per row, conflict-free for 8-byte accesses)
 //   B: H-pass result 64 x 64, row stride 65
+#ifndef RT_POST_SCALAR_BLUR
+#define RT_POST_SCALAR_BLUR 0
+#endif
 constexpr int kPairW = 64, kPairH = 56, kPairR = 4;
 constexpr int kPairAW = kPairW + 2 * kPairR, kPairAH = kPairH + 2 * kPairR;      // 72 x 64
 constexpr int kPairAStride = kPairAW + 1, kPairBStride = kPairW + 1;
 constexpr int kPairSeg = 4;                                                       // 4 x 64 = 256 threads
 constexpr int kPairHRun = kPairW / kPairSeg, kPairVRun = kPairH / kPairSeg;        // 16, 14
 constexpr size_t kPairSmem = (size_t)(kPairAH * kPairAStride + kPairAH * kPairBStride) * sizeof(uint2);
+
+// Packed FP32 pairs (FMUL2 / FFMA2 of sm_100: two IEEE round-to-nearest operations per issue slot). The blur pair is bound
+// by FP32 issue (51 multiply / add per output texel and pass, unfused by contract: gaussian_blurFs.glsl:12-22 rounds every
+// `texel * weight` before adding it), so both passes run on pairs: a lane filters TWO rows (columns) at once, holding each
+// texel's (r, g) as one pair and the two lines' b values as another.
+__device__ __forceinline__ float2 pmul2(float2 a, float2 b) {
+  float2 r;
+  asm("{ .reg .b64 ra, rb, rc; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; mul.rn.f32x2 rc, ra, rb; mov.b64 {%0, %1}, rc; }"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return r;
+}
+// a + b on pairs, written as fma(a, 1, b): the product a * 1 is exact, so the single rounding is add.rn's. It has to be
+// spelled this way because ptxas 12.9 contracts a mul.rn.f32x2 feeding an add.rn.f32x2 into ONE FFMA2 even with
+// --fmad=false (it honours the explicit .rn only for scalar f32; SASS inspected) — that would drop the rounding of the
+// product. The 1 comes from constant memory so that it stays a run-time value (a literal 1.0 is folded back into an add
+// and fused again).
+__constant__ float c_one = 1.0f;
+__device__ __forceinline__ float2 padd2(float2 a, float2 b) {
+  float2 r;
+  const float one = c_one;
+  asm("{ .reg .b64 ra, rb, rc, ro; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; mov.b64 ro, {%6, %6}; fma.rn.f32x2 rc, ra, ro, rb; mov.b64 {%0, %1}, rc; }"
+      : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(one));
+  return r;
+}
+// One tap position of two lines: (r, g) of line 0, (r, g) of line 1, (b of line 0, b of line 1).
+struct Tap2 { float2 rg0, rg1, bb; };
+__device__ __forceinline__ Tap2 tap2(uint2 q0, uint2 q1) {
+  Tap2 t;
+  t.rg0 = __half22float2(*reinterpret_cast<const __half2*>(&q0.x));
+  t.rg1 = __half22float2(*reinterpret_cast<const __half2*>(&q1.x));
+  t.bb = make_float2(__low2float(*reinterpret_cast<const __half2*>(&q0.y)), __low2float(*reinterpret_cast<const __half2*>(&q1.y)));
+  return t;
+}
+// blur9 of both lines: centre, then (+i, -i) for i = 1..4 — the shader's order, per channel.
+__device__ __forceinline__ void blur9x2(const Tap2 (&win)[9], f3& out0, f3& out1) {
+  const float2 w0 = make_float2(c_blur_w[0], c_blur_w[0]);
+  float2 a0 = pmul2(win[4].rg0, w0), a1 = pmul2(win[4].rg1, w0), ab = pmul2(win[4].bb, w0);
+#pragma unroll
+  for (int i = 1; i < 5; ++i) {
+    const float2 wi = make_float2(c_blur_w[i], c_blur_w[i]);
+    a0 = padd2(a0, pmul2(win[4 + i].rg0, wi)); a1 = padd2(a1, pmul2(win[4 + i].rg1, wi)); ab = padd2(ab, pmul2(win[4 + i].bb, wi));
+    a0 = padd2(a0, pmul2(win[4 - i].rg0, wi)); a1 = padd2(a1, pmul2(win[4 - i].rg1, wi)); ab = padd2(ab, pmul2(win[4 - i].bb, wi));
+  }
+  out0 = mk(a0.x, a0.y, ab.x);
+  out1 = mk(a1.x, a1.y, ab.y);
+}
 
 // centre, then (+i, -i) for i = 1..4: the shader's order. win[4] is the centre tap.
 __device__ __forceinline__ f3 blur9(const f3 (&win)[9]) {
@@ -253,7 +302,10 @@ __device__ __forceinline__ f3 blur9(const f3 (&win)[9]) {
 }
 
 template <bool FIRST, bool LAST>
-__global__ void __launch_bounds__(256, 3) blur_pair_kernel(const void* __restrict__ in, const float4* __restrict__ color,
+#ifndef RT_POST_PAIR_MINB
+#define RT_POST_PAIR_MINB 3
+#endif
+__global__ void __launch_bounds__(256, RT_POST_PAIR_MINB) blur_pair_kernel(const void* __restrict__ in, const float4* __restrict__ color,
                                                         void* __restrict__ out, int w, int h, float threshold, float strength) {
   extern __shared__ uint2 pair_smem[];
   uint2* A = pair_smem;
@@ -296,6 +348,7 @@ __global__ void __launch_bounds__(256, 3) blur_pair_kernel(const void* __restric
     }
   }
   __syncthreads();
+#if RT_POST_SCALAR_BLUR
   const int lane_item = threadIdx.x & 63, seg = threadIdx.x >> 6;
   // ---- horizontal pass: one lane per row of A, a run of 16 outputs
   {
@@ -338,6 +391,67 @@ __global__ void __launch_bounds__(256, 3) blur_pair_kernel(const void* __restric
       }
     }
   }
+#else
+  const int l32 = threadIdx.x & 31, seg8 = threadIdx.x >> 5;
+  // ---- horizontal pass: one lane per PAIR of rows of A (l and l + 32: the odd row stride keeps the 8-byte accesses of
+  // a half-warp on distinct banks), a run of 8 outputs per row, FP32 work on packed pairs (blur9x2)
+  {
+    constexpr int kRun = kPairW / 8;                       // 8 segments x 8 outputs
+    const uint2* row0 = A + l32 * kPairAStride + seg8 * kRun;
+    const uint2* row1 = row0 + 32 * kPairAStride;
+    uint2* dst0 = B + l32 * kPairBStride + seg8 * kRun;
+    uint2* dst1 = dst0 + 32 * kPairBStride;
+    Tap2 win[9];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) win[k + 1] = tap2(row0[k], row1[k]);
+#pragma unroll
+    for (int c = 0; c < kRun; ++c) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) win[k] = win[k + 1];
+      win[8] = tap2(row0[c + 8], row1[c + 8]);
+      f3 o0, o1;
+      blur9x2(win, o0, o1);
+      dst0[c] = pack_half_rgb1(o0);
+      dst1[c] = pack_half_rgb1(o1);
+    }
+  }
+  __syncthreads();
+  // ---- vertical pass: one lane per PAIR of columns of B (l and l + 32), a run of 7 outputs per column
+  {
+    constexpr int kRun = kPairH / 8;                       // 8 segments x 7 outputs
+    static_assert(kPairH % 8 == 0 && kPairAH == 64 && kPairW == 64, "pair kernel shape");
+    const int gx0 = x0 + l32, gx1 = gx0 + 32;
+    const uint2* col = B + (seg8 * kRun) * kPairBStride + l32;
+    Tap2 win[9];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) win[k + 1] = tap2(col[k * kPairBStride], col[k * kPairBStride + 32]);
+#pragma unroll
+    for (int r = 0; r < kRun; ++r) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) win[k] = win[k + 1];
+      win[8] = tap2(col[(r + 8) * kPairBStride], col[(r + 8) * kPairBStride + 32]);
+      const int gy = y0 + seg8 * kRun + r;
+      f3 o0, o1;
+      blur9x2(win, o0, o1);
+      const uint2 q0 = pack_half_rgb1(o0), q1 = pack_half_rgb1(o1);
+      if (gy < h) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int gx = half ? gx1 : gx0;
+          const uint2 q = half ? q1 : q0;
+          if (gx >= w) continue;
+          const size_t at = (size_t)gy * w + gx;
+          if (LAST) {                                      // bloom_combineFs.glsl on the rounded result
+            const f3 s = ld_f32_rgb(color, at), b = half_rgb(q);
+            static_cast<float4*>(out)[at] = make_float4(s.x + b.x * strength, s.y + b.y * strength, s.z + b.z * strength, 1.0f);
+          } else {
+            static_cast<uint2*>(out)[at] = q;
+          }
+        }
+      }
+    }
+  }
+#endif
 }
 
 // bloom_combineFs.glsl

@@ -6,7 +6,7 @@ import csv, io, json, os, re, subprocess, sys
 
 rep, key, source = sys.argv[1], sys.argv[2], sys.argv[3]
 pat = re.compile(sys.argv[4] if len(sys.argv) > 4 else r"rt_packet_kernel|wf_")
-out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr = rows[0]
 col = {k: hdr.index(k) for k in ("Kernel Name", "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
