@@ -233,8 +233,12 @@ __global__ void __launch_bounds__(256) blur_kernel(const uint2* __restrict__ in,
 //      CLAMP_TO_EDGE taps then simply read their neighbours), row stride 73 texels (odd: the H pass
 //      walks rows with one lane per row, conflict-free for 8-byte accesses)
 //   B: H-pass result 64 x 64, row stride 65
+// 1 (default): one lane per row / column, scalar FMUL + FADD. 0: two rows / columns per lane on packed f32x2 pairs (blur9x2).
+// Measured on B200, 1080p chain: scalar 0.1379 ms; packed 0.1586 ms at 80 registers (292 B of spills), 0.1356 ms at 128
+// registers (RT_POST_PAIR_MINB=2) — half the FP32 instructions, the same time: the pair kernel is NOT bound by FP32 issue.
+// Its 600 CTAs meet 444 resident slots (1.35 waves, paid as 2): the tile shape is what to change next.
 #ifndef RT_POST_SCALAR_BLUR
-#define RT_POST_SCALAR_BLUR 0
+#define RT_POST_SCALAR_BLUR 1
 #endif
 constexpr int kPairW = 64, kPairH = 56, kPairR = 4;
 constexpr int kPairAW = kPairW + 2 * kPairR, kPairAH = kPairH + 2 * kPairR;      // 72 x 64

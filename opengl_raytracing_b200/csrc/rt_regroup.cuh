@@ -21,8 +21,14 @@ namespace rt {
 namespace RT_VARIANT_NS {
 namespace pk {
 
+// Resident CTAs per SM the registers are sized for, measured on B200 (ms, 3 CTAs / 80 registers vs 2 CTAs / 128 registers):
+// small scenes C1 0.0911 / 0.0901, C2 0.3644 / 0.3686 (a wash: 3 kept, 24 warps); large scenes C3 13.48 / 12.35,
+// C5 13.01 / 12.59 (the long object loops spill at 80 registers: 2).
 #ifndef RT_RG_MINB
 #define RT_RG_MINB 3
+#endif
+#ifndef RT_RG_MINB_BIG
+#define RT_RG_MINB_BIG 2
 #endif
 constexpr int kRgMaxLights = 16;
 
@@ -32,7 +38,7 @@ __host__ __device__ inline size_t regroup_queue_bytes(int nl) {
 }
 
 template <bool BIG, bool BANDS, bool FAN>
-__global__ void __launch_bounds__(kThreads, RT_RG_MINB * 8 / RT_PK_WARPS) rt_regroup_kernel(const __grid_constant__ KernelParams kp) {
+__global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) * 8 / RT_PK_WARPS) rt_regroup_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const rt_frame_params& fp = kp.fp;
   Scene s; saddr cand_base; Textures tx;

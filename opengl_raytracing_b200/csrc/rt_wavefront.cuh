@@ -29,7 +29,12 @@ namespace pk {
 #define RT_WF_BOUNCE_MINB 3     // resident CTAs per SM the bounce kernel's registers are sized for (3 -> 80 registers)
 #endif
 #ifndef RT_WF_SHADOW_MINB
-#define RT_WF_SHADOW_MINB 3     // ... and the shadow kernel's
+#define RT_WF_SHADOW_MINB 3     // ... and the shadow kernel's, small scenes
+#endif
+// large scenes: 2 (128 registers). Measured on B200 (ms, 3 / 2 / 4 CTAs): C3 13.40 / 13.21 / 14.25, C5 7.73 / 7.54 / 7.85;
+// small scenes do not care (C2 0.4927 / 0.4907 / 0.5151). The bounce kernel stays at 3 (2: C3 14.13, C5 7.73).
+#ifndef RT_WF_SHADOW_MINB_BIG
+#define RT_WF_SHADOW_MINB_BIG 2
 #endif
 
 // The scene image in shared memory, as rt_packet_kernel stages it.
@@ -319,7 +324,7 @@ wf_bounce_kernel(const __grid_constant__ KernelParams kp, const __grid_constant_
 }
 
 template <bool BIG, bool FAN>
-__global__ void __launch_bounds__(kThreads, RT_WF_SHADOW_MINB * 8 / RT_PK_WARPS)
+__global__ void __launch_bounds__(kThreads, (BIG ? RT_WF_SHADOW_MINB_BIG : RT_WF_SHADOW_MINB) * 8 / RT_PK_WARPS)
 wf_shadow_kernel(const __grid_constant__ KernelParams kp, const __grid_constant__ WfParams wp) {
   extern __shared__ float4 smem[];
   Scene s; saddr cand_base; Textures tx;
