@@ -476,7 +476,14 @@ def run_ours(args) -> None:
         for p in h.values():
             ctx.lib.rt_host_free(p)
 
-    sub = multi_gpu_subrecords(args, rank, world, local) if (world > 1 and not args.no_subrecords) else None
+    sub = None
+    if world > 1 and not args.no_subrecords:
+        try:                                           # the sub-records must never cost the headline line
+            sub = multi_gpu_subrecords(args, rank, world, local)
+        except Exception as e:                         # noqa: BLE001 (every rank fails alike: same code, same inputs)
+            import traceback
+            traceback.print_exc()
+            sub = {"subrecords_error": f"{type(e).__name__}: {e}"}
 
     if rank == 0:
         peaks = {}
@@ -578,8 +585,7 @@ def multi_gpu_subrecords(args, rank: int, world: int, local: int) -> dict:
         """Choose the variant on a 1-sample frame of the same shape (seconds, not minutes) and pin it."""
         ctx.set_autotune(False)
         t = ctx.tune(workload_params(w, num_samples=1, **over))
-        ctx.set_tuning({"megakernel": abi.KERNEL_MEGAKERNEL, "wavefront": abi.KERNEL_WAVEFRONT}[t["kernel"]],
-                       1 if t["registers"] == 80 else 0, t["phase_level"])
+        ctx.set_tuning(abi.KERNEL_IDS[t["kernel"]], 1 if t["registers"] == 80 else 0, t["phase_level"])
         return t
 
     # ---- C4: sample ranges

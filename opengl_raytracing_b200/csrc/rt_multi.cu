@@ -53,15 +53,29 @@ __global__ void __launch_bounds__(256) peer_reduce_kernel(const __grid_constant_
     __syncthreads();
     if (s_bad) { if (threadIdx.x == 0) a.flags[a.rank][33] = 1u; return; }
   }
+  // two pixels per thread and iteration, every load issued before the first use: with N partials that is 2 N 16-byte
+  // loads in flight per thread — what hides the NVLink round trip (the kernel moves (N + 1) x 16 B per pixel and is bound
+  // by latency x bytes in flight, not by arithmetic)
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-  for (unsigned long long px = a.begin + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; px < a.end; px += stride) {
-    float4 v[RT_MAX_PEERS];
+  for (unsigned long long px = a.begin + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; px < a.end; px += 2 * stride) {
+    const unsigned long long px2 = px + stride;
+    const bool two = px2 < a.end;
+    float4 v[RT_MAX_PEERS], w[RT_MAX_PEERS];
 #pragma unroll
-    for (int r = 0; r < RT_MAX_PEERS; ++r) if (r < a.world) v[r] = ld_volatile_f4(a.partial[r] + px);   // all loads in flight, then the ordered sum
+    for (int r = 0; r < RT_MAX_PEERS; ++r) if (r < a.world) {
+      v[r] = ld_volatile_f4(a.partial[r] + px);
+      if (two) w[r] = ld_volatile_f4(a.partial[r] + px2);
+    }
     float x = v[0].x, y = v[0].y, z = v[0].z;
 #pragma unroll
-    for (int r = 1; r < RT_MAX_PEERS; ++r) if (r < a.world) { x = x + v[r].x; y = y + v[r].y; z = z + v[r].z; }
+    for (int r = 1; r < RT_MAX_PEERS; ++r) if (r < a.world) { x = x + v[r].x; y = y + v[r].y; z = z + v[r].z; }   // rank order: deterministic
     a.result[px] = make_float4(x * a.scale, y * a.scale, z * a.scale, 1.0f);
+    if (two) {
+      x = w[0].x; y = w[0].y; z = w[0].z;
+#pragma unroll
+      for (int r = 1; r < RT_MAX_PEERS; ++r) if (r < a.world) { x = x + w[r].x; y = y + w[r].y; z = z + w[r].z; }
+      a.result[px2] = make_float4(x * a.scale, y * a.scale, z * a.scale, 1.0f);
+    }
   }
   if (a.use_flags) {
     __threadfence_system();
@@ -83,8 +97,10 @@ __global__ void __launch_bounds__(256) peer_reduce_kernel(const __grid_constant_
 cudaError_t launch_peer_reduce(const PeerArgs& a, int sm_count, cudaStream_t stream) {
   if (a.end <= a.begin && !a.use_flags) return cudaSuccess;
   const unsigned long long px = a.end > a.begin ? a.end - a.begin : 0;
-  unsigned ctas = (unsigned)((px + 255) / 256);
-  const unsigned cap = (unsigned)(sm_count > 0 ? sm_count : 148) * 2u;   // co-resident by construction: the done protocol counts CTAs
+  unsigned ctas = (unsigned)((px + 511) / 512);
+  // a full machine of CTAs (8 x 256 threads per SM). No CTA waits for another CTA of its own grid — only for the peers'
+  // flags, which each peer's CTA 0 (always in its first wave) sets — so the grid need not be co-resident.
+  const unsigned cap = (unsigned)(sm_count > 0 ? sm_count : 148) * 8u;
   if (ctas > cap) ctas = cap;
   if (ctas < 1) ctas = 1;
   peer_reduce_kernel<<<ctas, 256, 0, stream>>>(a);

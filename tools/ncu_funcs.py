@@ -10,7 +10,9 @@ import subprocess
 import sys
 import tempfile
 
-MAJOR = ["trace_any_packet", "trace_one", "trace_any_one", "trace_closest_generic", "trace_closest", "shadow_packets",
+MAJOR = ["scan_candidates", "probe_fan", "cone_misses_sphere", "cone_misses_plane", "grid_cell", "wf_shadow_kernel", "wf_bounce_kernel",
+         "rt_regroup_kernel", "wf_light_vector", "wf_finish_pixel", "wf_stage_scene", "cosine_hemisphere", "refraction_dir", "random2",
+         "trace_any_packet", "trace_one", "trace_any_one", "trace_closest_generic", "trace_closest", "shadow_packets",
          "compute_lighting", "shade_pixel", "rt_packet_kernel", "subsurface", "compute_pbr", "fetch_sky", "fetch_noise",
          "trace_any", "pcf_shadow", "pcss_shadow", "rt_render_kernel", "load_light", "load_material"]
 
@@ -31,6 +33,9 @@ def main():
     ranges = {os.path.basename(header): func_ranges(header)}
     mh = os.path.join(os.path.dirname(header), "rt_math.cuh")
     if os.path.isfile(mh): ranges["rt_math.cuh"] = func_ranges(mh)
+    for extra in ("rt_packet.cuh", "rt_wavefront.cuh", "rt_regroup.cuh", "rt_kernel.cuh"):
+        eh = os.path.join(os.path.dirname(header), extra)
+        if os.path.isfile(eh) and extra not in ranges: ranges[extra] = func_ranges(eh)
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     hdr = rows[1]
