@@ -2,6 +2,7 @@
 // peer pull-reduce kernel of the sample-range sharding — the path's ONE real exchange step —
 // written over peer memory (NVLink loads / stores) instead of an NCCL call.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -42,69 +43,85 @@ __device__ bool wait_epoch(const unsigned* p, unsigned epoch) {
 // Rank r's share of the reduce: out[px] = (sum over ranks, IN RANK ORDER, of partial[rank][px].rgb) * scale, alpha 1,
 // for px in its slice. use_flags: the cross-process protocol of rt_peer_reduce (arrive / wait / done through flag
 // words in peer memory); without, the launch is already ordered behind every render by CUDA events (rt_multi).
+// WORLD is a template parameter so that the per-rank registers are exactly WORLD float4 per pixel in flight; PX pixels
+// per thread and iteration, every load issued before the first use: PX * WORLD 16-byte loads in flight per thread are
+// what hides the NVLink round trip (the kernel moves (WORLD + 1) x 16 B per pixel and is bound by latency x bytes in
+// flight, not by arithmetic).
+template <int WORLD, int PX>
 __global__ void __launch_bounds__(256) peer_reduce_kernel(const __grid_constant__ PeerArgs a) {
   __shared__ int s_bad;
+  const int world = a.world;                                        // <= WORLD: the instantiation is the next power of two
   if (a.use_flags) {
     // everything this rank enqueued before the kernel (its render) is complete and visible: tell every peer
-    if (blockIdx.x == 0 && threadIdx.x < a.world) st_release_sys(a.flags[threadIdx.x] + a.rank, a.epoch);
+    if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys(a.flags[threadIdx.x] + a.rank, a.epoch);
     if (threadIdx.x == 0) s_bad = 0;
     __syncthreads();
-    if (threadIdx.x < a.world && !wait_epoch(a.flags[a.rank] + threadIdx.x, a.epoch)) s_bad = 1;
+    if (threadIdx.x < world && !wait_epoch(a.flags[a.rank] + threadIdx.x, a.epoch)) s_bad = 1;
     __syncthreads();
     if (s_bad) { if (threadIdx.x == 0) a.flags[a.rank][33] = 1u; return; }
   }
-  // two pixels per thread and iteration, every load issued before the first use: with N partials that is 2 N 16-byte
-  // loads in flight per thread — what hides the NVLink round trip (the kernel moves (N + 1) x 16 B per pixel and is bound
-  // by latency x bytes in flight, not by arithmetic)
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-  for (unsigned long long px = a.begin + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; px < a.end; px += 2 * stride) {
-    const unsigned long long px2 = px + stride;
-    const bool two = px2 < a.end;
-    float4 v[RT_MAX_PEERS], w[RT_MAX_PEERS];
+  for (unsigned long long px0 = a.begin + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; px0 < a.end; px0 += PX * stride) {
+    float4 v[PX][WORLD];
 #pragma unroll
-    for (int r = 0; r < RT_MAX_PEERS; ++r) if (r < a.world) {
-      v[r] = ld_volatile_f4(a.partial[r] + px);
-      if (two) w[r] = ld_volatile_f4(a.partial[r] + px2);
+    for (int k = 0; k < PX; ++k) {
+      const unsigned long long px = px0 + k * stride;
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) if (r < world && px < a.end) v[k][r] = ld_volatile_f4(a.partial[r] + px);
     }
-    float x = v[0].x, y = v[0].y, z = v[0].z;
 #pragma unroll
-    for (int r = 1; r < RT_MAX_PEERS; ++r) if (r < a.world) { x = x + v[r].x; y = y + v[r].y; z = z + v[r].z; }   // rank order: deterministic
-    a.result[px] = make_float4(x * a.scale, y * a.scale, z * a.scale, 1.0f);
-    if (two) {
-      x = w[0].x; y = w[0].y; z = w[0].z;
+    for (int k = 0; k < PX; ++k) {
+      const unsigned long long px = px0 + k * stride;
+      if (px >= a.end) break;
+      float x = v[k][0].x, y = v[k][0].y, z = v[k][0].z;
 #pragma unroll
-      for (int r = 1; r < RT_MAX_PEERS; ++r) if (r < a.world) { x = x + w[r].x; y = y + w[r].y; z = z + w[r].z; }
-      a.result[px2] = make_float4(x * a.scale, y * a.scale, z * a.scale, 1.0f);
+      for (int r = 1; r < WORLD; ++r) if (r < world) { x = x + v[k][r].x; y = y + v[k][r].y; z = z + v[k][r].z; }   // rank order: deterministic
+      a.result[px] = make_float4(x * a.scale, y * a.scale, z * a.scale, 1.0f);
     }
   }
   if (a.use_flags) {
-    __threadfence_system();
+    // bar.sync orders every thread's stores before thread 0; its system-scope fence is cumulative: ONE fence per CTA
     __syncthreads();
     if (threadIdx.x == 0) {
+      __threadfence_system();
       unsigned* counter = a.flags[a.rank] + 32;
       if (atomicAdd(counter, 1u) == gridDim.x - 1) {           // the last CTA of this rank: the slice is in rank 0's frame
         *counter = 0u;
         __threadfence_system();
         st_release_sys(a.flags[0] + 16 + a.rank, a.epoch);
         if (a.rank == 0)
-          for (int r = 0; r < a.world; ++r)
+          for (int r = 0; r < world; ++r)
             if (!wait_epoch(a.flags[0] + 16 + r, a.epoch)) a.flags[0][33] = 1u;
       }
     }
   }
 }
 
+// dev knobs (read once): RT_PR_CTAS = CTAs per SM of the reduce grid, RT_PR_PX = pixels per thread and iteration (1, 2, 4)
+int knob(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+
+template <int WORLD>
+cudaError_t launch_peer_reduce_w(const PeerArgs& a, unsigned ctas, int px, cudaStream_t stream) {
+  if (px >= 4) peer_reduce_kernel<WORLD, 4><<<ctas, 256, 0, stream>>>(a);
+  else if (px == 2) peer_reduce_kernel<WORLD, 2><<<ctas, 256, 0, stream>>>(a);
+  else peer_reduce_kernel<WORLD, 1><<<ctas, 256, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_peer_reduce(const PeerArgs& a, int sm_count, cudaStream_t stream) {
   if (a.end <= a.begin && !a.use_flags) return cudaSuccess;
+  static const int per_sm = knob("RT_PR_CTAS", 4), ppt = knob("RT_PR_PX", 2);
   const unsigned long long px = a.end > a.begin ? a.end - a.begin : 0;
-  unsigned ctas = (unsigned)((px + 511) / 512);
-  // a full machine of CTAs (8 x 256 threads per SM). No CTA waits for another CTA of its own grid — only for the peers'
-  // flags, which each peer's CTA 0 (always in its first wave) sets — so the grid need not be co-resident.
-  const unsigned cap = (unsigned)(sm_count > 0 ? sm_count : 148) * 8u;
+  unsigned ctas = (unsigned)((px + 256ull * ppt - 1) / (256ull * ppt));
+  // No CTA waits for another CTA of its own grid — only for the peers' flags, which each peer's CTA 0 (always in its
+  // first wave) sets — so the grid need not be co-resident.
+  const unsigned cap = (unsigned)(sm_count > 0 ? sm_count : 148) * (unsigned)(per_sm > 0 ? per_sm : 4);
   if (ctas > cap) ctas = cap;
   if (ctas < 1) ctas = 1;
-  peer_reduce_kernel<<<ctas, 256, 0, stream>>>(a);
-  return cudaGetLastError();
+  if (a.world <= 2) return launch_peer_reduce_w<2>(a, ctas, ppt, stream);
+  if (a.world <= 4) return launch_peer_reduce_w<4>(a, ctas, ppt, stream);
+  if (a.world <= 8) return launch_peer_reduce_w<8>(a, ctas, ppt, stream);
+  return launch_peer_reduce_w<RT_MAX_PEERS>(a, ctas, ppt < 2 ? ppt : 2, stream);
 }
 
 void slice_of(unsigned long long pixels, int rank, int world, unsigned long long& b, unsigned long long& e) {
