@@ -5,13 +5,15 @@ usage: python tools/ncu_executed.py report.ncu-rep 'C3@3840x2160' 'profiles/r02_
 import csv, io, json, os, re, subprocess, sys
 
 rep, key, source = sys.argv[1], sys.argv[2], sys.argv[3]
-pat = re.compile(sys.argv[4] if len(sys.argv) > 4 else r"rt_packet_kernel|wf_")
+pat = re.compile(sys.argv[4] if len(sys.argv) > 4 else r"rt_packet_kernel|rt_regroup_kernel|wf_")
 out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr = rows[0]
-col = {k: hdr.index(k) for k in ("Kernel Name", "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
-                                 "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum", "smsp__inst_executed.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-                                 "gpu__time_duration.sum")}
+# ncu's raw page reports the FP32 opcode counters as per-cycle rates: count = <op>.sum.per_cycle_elapsed x smsp__cycles_elapsed.avg
+NAMES = ("Kernel Name", "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed",
+         "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed", "smsp__cycles_elapsed.avg", "smsp__inst_executed.sum",
+         "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__time_duration.sum")
+col = {k: hdr.index(k) for k in NAMES}
 units = rows[1]
 def num(r, k):
     v = float(r[col[k]].replace(",", "") or 0)
@@ -24,9 +26,10 @@ for r in rows[2:]:
     if not pat.search(name):
         continue
     kernels[name] = kernels.get(name, 0) + 1
-    acc["fadd"] += num(r, "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum")
-    acc["fmul"] += num(r, "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum")
-    acc["ffma"] += num(r, "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum")
+    cyc = num(r, "smsp__cycles_elapsed.avg")
+    acc["fadd"] += num(r, "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed") * cyc
+    acc["fmul"] += num(r, "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed") * cyc
+    acc["ffma"] += num(r, "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed") * cyc
     acc["warp_inst"] += num(r, "smsp__inst_executed.sum")
     acc["dram_read"] += num(r, "dram__bytes_read.sum")
     acc["dram_write"] += num(r, "dram__bytes_write.sum")
