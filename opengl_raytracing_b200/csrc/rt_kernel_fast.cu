@@ -27,7 +27,7 @@ cudaError_t launch_wf_shadow_fast(const KernelParams& kp, const WfParams& wp, in
   return fast::pk::launch_wf_shadow(kp, wp, sm_count, stream);
 }
 size_t packet_smem_bytes(int pk_float4s) {
-  return (size_t)pk_float4s * sizeof(float4) + (size_t)fast::pk::kCandCap * fast::pk::kThreads * 2;
+  return (size_t)pk_float4s * sizeof(float4) + (size_t)fast::pk::kScratchBytes;
 }
 bool wavefront_supported(const KernelParams& kp) {
   return kp.sc.pk_float4s > 0 && kp.sc.num_lights <= kWfMaxLights && kp.fp.max_ray_depth <= kWfMaxDepth &&

@@ -103,6 +103,7 @@ struct Scene {
   float maxd;
   const float4* grid;         // global memory: light grids (rt_abi.cu build_light_grids), nullptr = none
   int grid_off_f4, grid_ent_f4;
+  saddr wlist;                // this WARP's shared candidate lists (cooperative cluster scan), 0 = none
 };
 
 __device__ __forceinline__ float lds32(saddr p) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(p)); return v; }
@@ -175,7 +176,9 @@ __device__ __forceinline__ int hit_object_index(const Scene& s, int code) {
 // Dev-only statistics build (-DRT_PK_STATS=1): per-thread atomics into kp.counters, read with
 // rt_get_counters. 0 jobs, 1 jobs with no candidate, 2 overflow jobs, 3 candidates (list jobs),
 // 4 prescan cone tests, 5 packets traced, 6 packet-loop object visits, 7 closest rays,
-// 8 cluster slab tests, 9 member slab tests, 10 closest linear fallbacks
+// 8 cluster slab tests, 9 member slab tests, 10 closest linear fallbacks; cooperative scan, per warp: 11 converged warps,
+// 12 scans that produced a list, 13 clusters listed, 14 spheres listed, 15 not coherent, 16 / 17 cluster / sphere list overflow,
+// 18 entered (some lane wanted a cluster scan), 19 closest-hit warps that shared their scan
 #ifndef RT_PK_STATS
 #define RT_PK_STATS 0
 #endif
@@ -187,12 +190,142 @@ __device__ unsigned long long* g_stats;
 #endif
 
 constexpr int kCandCap = 32;          // per-thread scratch list (u16 codes) in shared memory
+#ifndef RT_PK_WCLUSTERS
+#define RT_PK_WCLUSTERS 128
+#endif
+#ifndef RT_PK_WSPHERES
+#define RT_PK_WSPHERES 64
+#endif
+// per-warp lists of the cooperative cluster scan (coop_cluster_scan): passing clusters, then passing sphere slots (u16 each)
+constexpr int kWarpClusterCap = RT_PK_WCLUSTERS, kWarpSphereCap = RT_PK_WSPHERES;
+constexpr int kWarpListBytes = (kWarpClusterCap + kWarpSphereCap) * 2;
+// dynamic shared memory behind the scene blob: the per-thread candidate lists, then the per-warp lists
+constexpr int kScratchBytes = kCandCap * kThreads * 2 + kWarpsPerCta * kWarpListBytes;
+static_assert(kScratchBytes % 16 == 0, "the regrouping kernel's queues follow the scratch as float4");
+#ifndef RT_PK_COOP
+#define RT_PK_COOP 2                  // 0 off, 1 shadow jobs, 2 + closest-hit rays
+#endif
 __device__ __forceinline__ void cand_store(saddr cand_base, int i, int code) {
   asm volatile("st.shared.u16 [%0], %1;" :: "r"(cand_base + (unsigned)i * (kThreads * 2u)), "h"((unsigned short)code) : "memory");
 }
 __device__ __forceinline__ int cand_load(saddr cand_base, int i) {
   unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(cand_base + (unsigned)i * (kThreads * 2u)) : "memory");
   return (int)v;
+}
+
+struct Cone { f3 L; float s, c2, far; f3 fn; float fe; bool fan; };   // axis, sin bound, cos^2 bound, far = lim*(1+e); fan plane normal (0 = none), PCF slack
+struct Cands { saddr base; int n, first, nsph; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test); list entries [first, n), the first nsph of [0, n) are spheres
+
+// FANSKIP: branch around the fan-plane test when the job has no probes. Worth about 1 % in the
+// small-scene kernel's sphere scan (same-box A/B on C2); in the large-scene kernel's long scan loops
+// the branch costs more than the 8 instructions it saves (C3 19.3 -> 20.3 ms): straight-line there.
+template <bool FANSKIP = false>
+__device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 center, float r) {
+  const f3 v = center - o;
+  const float along = fmaf(v.z, c.L.z, fmaf(v.y, c.L.y, v.x * c.L.x));
+  const float d2 = fmaf(v.z, v.z, fmaf(v.y, v.y, v.x * v.x));
+  const float rr = fabsf(r) * 1.001f;                       // a negative radius is the same sphere (glsl:108 squares it)
+  const float q = fmaf(along, c.s, rr);                     // r' + along*sin
+  const float lhs = fmaf(-along, along, d2) * c.c2;         // perp^2 * cos^2
+  const float rhs = fmaf(d2, 4.0e-6f, q * q);
+  if (q < 0.0f || lhs > rhs || along - rr > c.far) return true;      // any NaN: not culled
+  // PCSS fan: the 16 probes all lie in the plane through o spanned by L and (1,1,1) (glsl:409 adds
+  // the same scalar to x, y and z), the PCF samples within fe of L: a sphere farther than that from
+  // the plane is out of reach. fn = 0 (no probes, or L || (1,1,1)) disables the test.
+  if (FANSKIP && !c.fan) return false;                      // no probes in this job (or L || (1,1,1)): fn = 0, nothing to test
+  const float w = fmaf(v.z, c.fn.z, fmaf(v.y, c.fn.y, v.x * c.fn.x));
+  return fabsf(w) > fmaf(sqrtf(d2) * 1.001f + rr, c.fe, rr);
+}
+
+// ---- warp-cooperative cluster scan. The 32 rays (closest-hit) or shadow jobs a converged warp holds are usually neighbours
+// (the pixels of one tile; consecutive hits of one pixel block under one light): instead of 32 lanes each testing every
+// cluster and every member of the passing clusters on its own (C3: ~127 cone tests per wide-cone shadow job, 23 % of all
+// executed instructions; C5: 155 slab tests per primary ray), the warp scans ONCE against a cone that contains all of them
+// — one entry per lane and step — into a shared list, and every lane then runs its own exact tests on that short list.
+// The union: apex = the mean origin om, axis = the normalised mean of the axes Lm, sin = max_i(sin angle(L_i, Lm) + s_i),
+// far = max_i far_i + ro, and every radius grown by ro = max_i |o_i - om| (a ray point o_i + t d is within ro of om + t d,
+// which lies in the union cone). Only the lanes with `want` contribute; the others just help scanning. A lane's final set is
+// a subset of the shared one chosen by the SAME exact tests as before, so it is again a conservative superset of what its
+// rays can touch: identical images (shadow packets decide with the exact per-ray tests, an any-hit does not depend on the
+// order; the closest hit's tie rule is by original index, so its visiting order is free too).
+// Returns the list length, or -1 — every lane alike — when the wanting lanes are not coherent enough (sin >= 0.7, a
+// non-finite input, a list that overflows): the callers then scan per lane. All 32 lanes must call it together.
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ int lds_u16(saddr p) { unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(p) : "memory"); return (int)v; }
+__device__ __forceinline__ void sts_u16(saddr p, int v) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(p), "h"((unsigned short)v) : "memory"); }
+
+__device__ __noinline__ int coop_cluster_scan(saddr clu, saddr sph, int nc, int ns, saddr wl, bool want, f3 L, float cs, float cfar, f3 o) {
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  __syncwarp();                                                                      // every reader of the previous list is done
+  const float probe = ((o.x + o.y) + o.z) + ((L.x + L.y) + L.z) + cs;                // NaN / inf anywhere -> not finite
+  if (__any_sync(0xffffffffu, want && (!(fabsf(probe) < 3.0e38f) || cfar != cfar))) return -1;   // (a NaN far never culls: not unionable)
+  if (!want) { o = mk3(0.0f, 0.0f, 0.0f); L = o; cs = 0.0f; cfar = 0.0f; }
+  const float inv_n = 1.0f / (float)__popc(__ballot_sync(0xffffffffu, want));
+  const f3 om = mk3(warp_sum(o.x) * inv_n, warp_sum(o.y) * inv_n, warp_sum(o.z) * inv_n);
+  const f3 Ls = mk3(warp_sum(L.x), warp_sum(L.y), warp_sum(L.z));
+  const float ll = fmaf(Ls.z, Ls.z, fmaf(Ls.y, Ls.y, Ls.x * Ls.x));
+  if (!(ll > 0.25f)) { if (lane == 0) PK_STAT(15, 1); return -1; }                   // axes pointing apart: no common cone
+  const f3 Lm = Ls * rsqrtf(ll);
+  const f3 dv = want ? o - om : mk3(0.0f, 0.0f, 0.0f);
+  const float ro = warp_max(sqrtf(fmaf(dv.z, dv.z, fmaf(dv.y, dv.y, dv.x * dv.x)))) * 1.001f + 1.0e-6f * (1.0f + fabsf(om.x) + fabsf(om.y) + fabsf(om.z));
+  const f3 cx = cross3(L, Lm);                                                       // |L| in (0.995, 1.005) (callers), |Lm| = 1 up to rounding
+  const float S = warp_max(want ? sqrtf(fmaf(cx.z, cx.z, fmaf(cx.y, cx.y, cx.x * cx.x))) * 1.01f + cs : 0.0f) * 1.01f + 1.0e-5f;
+  const bool behind = want && !(fmaf(L.z, Lm.z, fmaf(L.y, Lm.y, L.x * Lm.x)) > 0.0f);   // sin alone cannot tell an axis from its opposite
+  if (!(S < 0.7f) || __any_sync(0xffffffffu, behind)) { if (lane == 0) PK_STAT(15, 1); return -1; }
+  Cone u;
+  u.L = Lm; u.s = S; u.c2 = (1.0f - S * S) * 0.999f; u.far = warp_max(cfar) + ro * 1.001f;
+  u.fn = mk3(0.0f, 0.0f, 0.0f); u.fe = 0.0f; u.fan = false;
+  // level 1: cluster bounding spheres
+  int n1 = 0;
+#pragma unroll 1
+  for (int c0 = 0; c0 < nc; c0 += 32) {
+    const int c = c0 + lane;
+    bool pass = false;
+    if (c < nc) {
+      const float4 q = lds128(clu + (unsigned)c * kSphereBytes + 48u);
+      pass = !cone_misses_sphere(u, om, xyz(q), fabsf(q.w) + ro);
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, pass);
+    const int at = n1 + __popc(b & lt);
+    if (pass && at < kWarpClusterCap) sts_u16(wl + 2u * (unsigned)at, c);
+    n1 += __popc(b);
+  }
+  if (n1 > kWarpClusterCap) { if (lane == 0) PK_STAT(16, 1); return -1; }
+  __syncwarp();
+  // level 2: the members of the passing clusters
+  int n2 = 0;
+  const int tot = n1 * kPkClusterSize;
+#pragma unroll 1
+  for (int i0 = 0; i0 < tot; i0 += 32) {
+    const int i = i0 + lane;
+    bool pass = false;
+    int k = 0;
+    if (i < tot) {
+      k = lds_u16(wl + 2u * (unsigned)(i / kPkClusterSize)) * kPkClusterSize + (i % kPkClusterSize);
+      if (k < ns) {
+        const float4 q = lds128(sph + (unsigned)k * kSphereBytes + 48u);
+        pass = !cone_misses_sphere(u, om, xyz(q), fabsf(q.w) + ro);
+      }
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, pass);
+    const int at = n2 + __popc(b & lt);
+    if (pass && at < kWarpSphereCap) sts_u16(wl + 2u * (unsigned)(kWarpClusterCap + at), k);
+    n2 += __popc(b);
+  }
+  if (n2 > kWarpSphereCap) { if (lane == 0) PK_STAT(17, 1); return -1; }
+  __syncwarp();
+  if (lane == 0) { PK_STAT(12, 1); PK_STAT(13, n1); PK_STAT(14, n2); }
+  return n2;
 }
 
 // Closest hit of one ray over the whole scene, the shader's tie rule (glsl:155-196): among equal
@@ -205,7 +338,7 @@ __device__ __forceinline__ int cand_load(saddr cand_base, int i) {
 // member box — the cluster test is exactly conservative, no tolerance involved. Passing clusters
 // go to the lane's scratch list, then each lane walks the members of its own clusters.
 template <bool GENERIC, bool BIG>
-__device__ __forceinline__ Hit trace_one(const Scene& s, saddr cand_base, f3 o, f3 d, f3 inv, float a) {
+__device__ __forceinline__ Hit trace_one(const Scene& s, saddr cand_base, f3 o, f3 d, f3 inv, float a, bool coop = false) {
   const unsigned offx = (!GENERIC && d.x < 0.0f) ? 8u : 0u;      // the (near,far) pair this ray's sign selects
   const unsigned offy = (!GENERIC && d.y < 0.0f) ? 24u : 16u;
   const unsigned offz = (!GENERIC && d.z < 0.0f) ? 40u : 32u;
@@ -234,7 +367,25 @@ __device__ __forceinline__ Hit trace_one(const Scene& s, saddr cand_base, f3 o, 
   };
   bool linear = true;
   PK_STAT(7, 1);
-  if (BIG && !GENERIC && s.nc > 0) {
+  // coop (warp-uniform; all 32 lanes are here together): one scan of the clusters for the whole warp against the cone that
+  // holds its 32 rays, then this ray's own slab + sphere tests on the short shared list. A ray that touches a sphere lies in
+  // the union cone and touches the bounding sphere the scan tests (with the margins of cone_misses_sphere), so the list holds
+  // every sphere the ray can hit.
+  int nshared = -1;
+  if (BIG && !GENERIC && RT_PK_COOP && coop) {
+    if ((threadIdx.x & 31) == 0) PK_STAT(19, 1);
+    nshared = coop_cluster_scan(s.clu, s.sph, s.nc, s.ns, s.wlist, true, d * rsqrtf(a), 2.0e-5f, 3.0e38f, o);
+  }
+  if (BIG && !GENERIC && nshared >= 0) {
+    linear = false;
+#pragma unroll 2
+    for (int i = 0; i < nshared; ++i) {
+      const int k = lds_u16(s.wlist + 2u * (unsigned)(kWarpClusterCap + i));
+      const saddr rec = s.sph + (unsigned)k * kSphereBytes;
+      PK_STAT(9, 1);
+      if (slab(rec + offx, rec + offy, rec + offz)) sphere(k);
+    }
+  } else if (BIG && !GENERIC && s.nc > 0) {
     int n = 0;
     PK_STAT(8, s.nc);
     saddr ax = s.clu + offx, ay = s.clu + offy, az = s.clu + offz;
@@ -295,6 +446,10 @@ template <bool BIG>
 __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3 o, f3 d) {
   const f3 inv = mk3(rcp_ieee(d.x), rcp_ieee(d.y), rcp_ieee(d.z));
   const float a = dot3(d, d);
+  // the whole warp is here, converged, every ray regular: the cluster scan is shared (see trace_one)
+  bool coop = false;
+  if (BIG && RT_PK_COOP >= 2 && s.nc > 0 && s.wlist != 0u && __activemask() == 0xffffffffu)
+    coop = __all_sync(0xffffffffu, dir_regular(d, a));
   if (!dir_regular(d, a)) {
     // rare path: the out-of-line routine takes COPIES, so that the structs of the common path are
     // never address-taken and stay in registers (a by-reference argument of a noinline function
@@ -302,7 +457,7 @@ __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3
     const Scene s2 = s;
     return trace_closest_generic(s2, o, d, inv, a);
   }
-  return trace_one<false, BIG>(s, cand_base, o, d, inv, a);
+  return trace_one<false, BIG>(s, cand_base, o, d, inv, a, coop);
 }
 
 // ---------------------------------------------------------------- shadow jobs: cone culling
@@ -317,29 +472,6 @@ __device__ __forceinline__ Hit trace_closest(const Scene& s, saddr cand_base, f3
 // Conservative: sin is over-, cos under-estimated, radii are inflated by 1e-3, and the squared
 // comparison carries a 4e-6*|v|^2 slack (40x the rounding of d2 - along^2, and above the
 // 1e-7*|v|^2 by which the shader's own discriminant can report a grazing hit).
-struct Cone { f3 L; float s, c2, far; f3 fn; float fe; bool fan; };   // axis, sin bound, cos^2 bound, far = lim*(1+e); fan plane normal (0 = none), PCF slack
-struct Cands { saddr base; int n, first, nsph; bool list, prefilter; };   // !list: scan every object (prefilter: with the cone test); list entries [first, n), the first nsph of [0, n) are spheres
-
-// FANSKIP: branch around the fan-plane test when the job has no probes. Worth about 1 % in the
-// small-scene kernel's sphere scan (same-box A/B on C2); in the large-scene kernel's long scan loops
-// the branch costs more than the 8 instructions it saves (C3 19.3 -> 20.3 ms): straight-line there.
-template <bool FANSKIP = false>
-__device__ __forceinline__ bool cone_misses_sphere(const Cone& c, f3 o, f3 center, float r) {
-  const f3 v = center - o;
-  const float along = fmaf(v.z, c.L.z, fmaf(v.y, c.L.y, v.x * c.L.x));
-  const float d2 = fmaf(v.z, v.z, fmaf(v.y, v.y, v.x * v.x));
-  const float rr = fabsf(r) * 1.001f;                       // a negative radius is the same sphere (glsl:108 squares it)
-  const float q = fmaf(along, c.s, rr);                     // r' + along*sin
-  const float lhs = fmaf(-along, along, d2) * c.c2;         // perp^2 * cos^2
-  const float rhs = fmaf(d2, 4.0e-6f, q * q);
-  if (q < 0.0f || lhs > rhs || along - rr > c.far) return true;      // any NaN: not culled
-  // PCSS fan: the 16 probes all lie in the plane through o spanned by L and (1,1,1) (glsl:409 adds
-  // the same scalar to x, y and z), the PCF samples within fe of L: a sphere farther than that from
-  // the plane is out of reach. fn = 0 (no probes, or L || (1,1,1)) disables the test.
-  if (FANSKIP && !c.fan) return false;                      // no probes in this job (or L || (1,1,1)): fn = 0, nothing to test
-  const float w = fmaf(v.z, c.fn.z, fmaf(v.y, c.fn.y, v.x * c.fn.x));
-  return fabsf(w) > fmaf(sqrtf(d2) * 1.001f + rr, c.fe, rr);
-}
 __device__ __forceinline__ bool cone_misses_plane(const Cone& c, f3 o, saddr rec) {
   const float4 pn = lds128(rec + 48u), pp = lds128(rec + 96u), pb = lds128(rec + 112u);
   const f3 n = xyz(pn);
@@ -400,12 +532,24 @@ __device__ __forceinline__ int grid_cell(const Scene& s, int light_index, const 
 // One scan of the scene per shadow job. Returns the candidate set for the job's packets.
 template <bool BIG>
 __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base, bool cone_ok, const Cone& cone, f3 o,
-                                                 int light_index, float lightDistance) {
+                                                 int light_index, float lightDistance, bool warp_converged) {
   Cands cd; cd.base = cand_base; cd.n = s.ns + s.np; cd.first = 0; cd.nsph = s.ns; cd.list = false; cd.prefilter = false;
+  int first_cell = 0, shared_cell = 0;
+  const int cell = (BIG && s.grid && cone_ok) ? grid_cell(s, light_index, cone, o, lightDistance, first_cell, shared_cell) : -1;
+  // warp_converged: the caller vouches that all 32 lanes of the warp get here, each with a job (of any light). When any
+  // of them is about to scan the clusters, the warp scans once, together (coop_cluster_scan); nshared < 0: each on its own.
+  int nshared = -1;
+  if (BIG && RT_PK_COOP && warp_converged) {
+    const bool want = cone_ok && s.nc > 0 && s.wlist != 0u && cell < 0;
+    if ((threadIdx.x & 31) == 0) PK_STAT(11, 1);
+    if (__any_sync(0xffffffffu, want)) {
+      if ((threadIdx.x & 31) == 0) PK_STAT(18, 1);
+      nshared = coop_cluster_scan(s.clu, s.sph, s.nc, s.ns, s.wlist, want, cone.L, cone.s, cone.far, o);
+      if (!want) nshared = -1;
+    }
+  }
   if (!cone_ok) return cd;
   int n = 0;
-  int first_cell = 0, shared_cell = 0;
-  const int cell = (BIG && s.grid) ? grid_cell(s, light_index, cone, o, lightDistance, first_cell, shared_cell) : -1;
   if (BIG && cell >= 0) {                                    // light grid: the cell's spheres + the shared list, exact cone test on each
     const unsigned* offs = reinterpret_cast<const unsigned*>(s.grid + s.grid_off_f4) + first_cell;
     const unsigned short* ents = reinterpret_cast<const unsigned short*>(s.grid + s.grid_ent_f4);
@@ -422,6 +566,16 @@ __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base
         if (n < kCandCap) cand_store(cand_base, n, k);
         ++n;
       }
+    }
+  } else if (BIG && nshared >= 0) {                          // the warp's shared list, filtered by this job's own exact cone test
+#pragma unroll 2
+    for (int i = 0; i < nshared; ++i) {
+      const int k = lds_u16(s.wlist + 2u * (unsigned)(kWarpClusterCap + i));
+      const float4 sp = lds128(s.sph + (unsigned)k * kSphereBytes + 48u);
+      PK_STAT(4, 1);
+      if (cone_misses_sphere(cone, o, xyz(sp), sp.w)) continue;
+      if (n < kCandCap) cand_store(cand_base, n, k);
+      ++n;
     }
   } else if (BIG && s.nc > 0) {                              // cluster bounding spheres first, then members
     saddr crec = s.clu;
@@ -451,6 +605,7 @@ __device__ __forceinline__ Cands scan_candidates(const Scene& s, saddr cand_base
       ++n;
     }
   }
+  // (the shared list is rewritten only behind the __syncwarp at the top of the warp's next coop_cluster_scan)
   cd.nsph = n;
   saddr rec = s.pln;
   for (int j = 0; j < s.np; ++j, rec += kPlaneBytes) {
@@ -652,9 +807,15 @@ __device__ __noinline__ int probe_fan(saddr sph, saddr cand_base, int nsph, f3 o
 // calculateShadow (glsl:442-455) for shadowType 1 (pcfShadow, glsl:342-397) and 2 (pcssShadow,
 // glsl:400-440 = "fully lit unless one of 16 fixed probes is blocked, else PCF"). Probes and PCF
 // samples run through ONE packet site: jobs [0,nprobe) are probes, [nprobe,nprobe+pcf) samples.
-template <bool BIG, bool FAN>
-__device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
-                                                int light_index, f3 lightDir, float lightDistance) {
+// MODE 0: the whole job. MODE 1: the prescan only — returns with done = true when the factor is already known (nothing in
+// the cone: 1.0), else done = false and the candidate set in cdio. MODE 2: the packets only, over the candidate set cdio
+// of an earlier MODE 1 call with the SAME arguments (cdio.base may be another thread's scratch list). Everything between
+// — the cone, the limits — is a pure function of the arguments, so 1 + 2 computes exactly what 0 does: the regrouping
+// megakernel (rt_regroup.cuh) uses the split to run the packets on survivors only.
+template <bool BIG, bool FAN, int MODE>
+__device__ __forceinline__ float shadow_packets_m(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
+                                                  int light_index, f3 lightDir, float lightDistance, Cands& cdio, bool& done,
+                                                  bool warp_converged = false) {
   const int nprobe = light.shadowType == 2 ? 16 : 0;
   const int total = nprobe + (light.pcfSamples > 0 ? light.pcfSamples : 0);
   const float filterSize = light.shadowSoftness * 0.005f;                        // glsl:364 (overwrites :352)
@@ -680,7 +841,12 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
   }
   const float ll = dot3(lightDir, lightDir);
   const bool cone_ok = (unsigned)light.type <= 2u && cone.s < 0.7f && ll > 0.99f && ll < 1.01f;
-  const Cands cd = scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin, light_index, lightDistance);
+  const Cands cd = MODE == 2 ? cdio : scan_candidates<BIG>(s, cand_base, cone_ok, cone, origin, light_index, lightDistance, warp_converged);
+  if (MODE == 1) {
+    cdio = cd;
+    done = cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0);
+    return 1.0f;
+  }
   if (cd.list && cd.n == 0 && (nprobe || light.pcfSamples > 0)) return 1.0f;    // nothing can occlude: n/n, or no blocker
   int unoccluded = 0;
   int j = 0;
@@ -749,6 +915,12 @@ __device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base,
     }
   }
   return div_ieee((float)unoccluded, (float)light.pcfSamples);     // 0/0 = NaN when pcfSamples == 0
+}
+template <bool BIG, bool FAN>
+__device__ __forceinline__ float shadow_packets(const Scene& s, saddr cand_base, float noise_r, f3 origin, const LightRec& light,
+                                                int light_index, f3 lightDir, float lightDistance, bool warp_converged = false) {
+  Cands cd; bool done;
+  return shadow_packets_m<BIG, FAN, 0>(s, cand_base, noise_r, origin, light, light_index, lightDir, lightDistance, cd, done, warp_converged);
 }
 
 // computeSubsurfaceScattering (glsl:316-339); unreachable from the reference's UI and scene files.
@@ -858,7 +1030,8 @@ __device__ __forceinline__ f3 compute_lighting(const Scene& s, saddr cand_base, 
     if (brdf.x == 0.0f && brdf.y == 0.0f && brdf.z == 0.0f && (!sampled || light.pcfSamples > 0)) continue;
     float shadowFactor = 0.0f;                           // calculateShadow (glsl:442-455)
     if (light.shadowType == 0) shadowFactor = 1.0f;
-    else if (sampled) shadowFactor = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, i, lightDir, lightDistance);
+    else if (sampled) shadowFactor = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, i, lightDir, lightDistance,
+                                                              RT_PK_COOP >= 1 && __activemask() == 0xffffffffu);
     Lo = smad3(brdf, shadowFactor, Lo);
   }
   if (lit && mat.subsurfaceScatter > 0.0f) {
@@ -1010,6 +1183,7 @@ __global__ void __launch_bounds__(kThreads, PK_MIN_CTAS(BIG, MINB)) rt_packet_ke
   s.grid = BIG ? sc.pk_grid : nullptr; s.grid_off_f4 = sc.pk_grid_off_f4; s.grid_ent_f4 = sc.pk_grid_ent_f4;
   // per-thread candidate list behind the scene image: entry i of thread t at +(i*kThreads + t)*2
   const saddr cand_base = base + (unsigned)sc.pk_float4s * 16u + threadIdx.x * 2u;
+  s.wlist = base + (unsigned)sc.pk_float4s * 16u + (unsigned)(kCandCap * kThreads * 2) + (threadIdx.x >> 5) * (unsigned)kWarpListBytes;
 
   Textures tx;
   tx.sky = sc.sky; tx.sky_tex = sc.sky_tex; tx.sky_size = sc.sky_size;
@@ -1094,7 +1268,7 @@ inline cudaError_t upload_probe_order(const float* halton3, const int* order16) 
 
 template <bool BIG, bool BANDS, int MINB, bool FAN>
 inline cudaError_t launch_packet_t(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
-  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
+  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kScratchBytes;
   int per_sm = 0;
   cudaError_t e = cached_occupancy(rt_packet_kernel<BIG, BANDS, MINB, FAN>, kThreads, smem, &per_sm);
   if (e != cudaSuccess) return e;

@@ -30,11 +30,17 @@ namespace pk {
 #ifndef RT_RG_MINB_BIG
 #define RT_RG_MINB_BIG 2
 #endif
+// RT_RG_SPLIT=1: round B in two phases (B1 prescan, B2 the packets of the surviving jobs on compacted lanes). Measured on
+// B200 and REJECTED: C1 0.088 -> 0.094, C2 0.360 -> 0.395, C3 12.37 -> 13.45 ms — three more CTA barriers per batch and
+// the recomputed job data cost more than the idle lanes of the one-pass form. Bit-identical either way.
+#ifndef RT_RG_SPLIT
+#define RT_RG_SPLIT 0
+#endif
 constexpr int kRgMaxLights = 16;
 
 // bytes of dynamic shared memory behind the scene blob and the candidate scratch, for nl lights
 __host__ __device__ inline size_t regroup_queue_bytes(int nl) {
-  return (size_t)kThreads * (3 * 16 + 2 * 16 + 16) + (size_t)(nl > 0 ? nl : 1) * kThreads * (16 + 1);
+  return (size_t)kThreads * (3 * 16 + 2 * 16 + 16 + 8) + (size_t)(nl > 0 ? nl : 1) * kThreads * (16 + 1);
 }
 
 template <bool BIG, bool BANDS, bool FAN>
@@ -45,16 +51,17 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
   wf_stage_scene<BIG>(kp, smem, s, cand_base, tx);
   const int nl = s.nl;
   // queue records behind the scene blob and the per-thread candidate lists (16-byte aligned: both are multiples of 16)
-  float4* q = smem + kp.sc.pk_float4s + (kCandCap * kThreads * 2) / 16;
+  float4* q = smem + kp.sc.pk_float4s + kScratchBytes / 16;
   float4* q_rd = q;                      // (rd, pixel bits)
   float4* q_tp = q + kThreads;           // (throughput, noise_r)
   float4* q_col = q + 2 * kThreads;      // (colour so far, block-local pixel bits)
   float4* h_p = q + 3 * kThreads;        // (P, object index bits)
   float4* h_n = q + 4 * kThreads;        // (N, contributing-light mask bits)
   float4* sum = q + 5 * kThreads;        // per pixel of the block: running colour sum over the samples
-  float4* brdf = q + 6 * kThreads;       // nl planes: (BRDF term, shadow factor)
+  uint2* surv_rec = reinterpret_cast<uint2*>(q + 6 * kThreads);   // round B: the surviving jobs of a batch (kThreads x 8 B = half a plane)
+  float4* brdf = q + 6 * kThreads + kThreads / 2;                 // nl planes: (BRDF term, shadow factor)
   unsigned char* jobq = reinterpret_cast<unsigned char*>(brdf + (size_t)(nl > 0 ? nl : 1) * kThreads);   // nl planes of hit slots
-  __shared__ unsigned s_tile, s_nhit, s_njob[kRgMaxLights];
+  __shared__ unsigned s_tile, s_nhit, s_njob[kRgMaxLights], s_wsurv[kWarpsPerCta];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned lt = (1u << lane) - 1u;
@@ -266,27 +273,76 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
         n_live = s_nhit;
         if (n_live == 0u) break;                         // uniform: every path of the block has ended
 
-        // ================= round B: the shadow jobs, light-major (a warp runs one light's code unless it straddles two)
+        // ================= round B: the shadow jobs, light-major, in batches of one job per lane
+        //   B1  every job runs its PRESCAN (light grid / cluster scan with the cone test -> the lane's candidate list). Jobs
+        //       with nothing in their cone are done: factor 1 (C2: half of all jobs). The survivors are compacted CTA-wide
+        //       in job order (still light-major: a warp of B2 runs one light's code).
+        //   B2  lane k < n_surv runs the PACKETS of survivor k, reading the candidate list where its owner lane left it.
+        // so the lanes that trace rays are consecutive and whole warps without survivors skip the packets (RT_RG_SPLIT=0:
+        // one pass, prescan and packets in the same lane — the A/B baseline).
         {
           unsigned total = 0;
           for (int l = 0; l < nl; ++l) total += s_njob[l];
+          // the job of index j: (light, hit slot) and everything shadow_packets needs — recomputed in B2 from the same records
+          auto job_of = [&](unsigned j, int& l, int& slot2, LightRec& light, float& nr, f3& origin, f3& lightDir, float& lightDistance) {
+            l = 0; unsigned jj = j;
+            while (jj >= s_njob[l]) { jj -= s_njob[l]; ++l; }
+            slot2 = (int)jobq[l * kThreads + (int)jj];
+            light = load_light(s, l);
+            const float4 h0 = h_p[slot2], h1 = h_n[slot2];
+            nr = q_tp[slot2].w;
+            float attenuation;
+            wf_light_vector(light, xyz(h0), lightDir, lightDistance, attenuation);
+            origin = smad3(xyz(h1), 0.001f, xyz(h0));                            // glsl:381, :412 (P + N * 0.001)
+          };
 #pragma unroll 1
           for (unsigned j0 = 0; j0 < total; j0 += kThreads) {
             const unsigned j = j0 + (unsigned)tid;
-            if (j0 + (unsigned)(warp * 32) >= total) break;         // whole warps beyond the job count skip the round
-            if (j < total) {
-              int l = 0; unsigned jj = j;
-              while (jj >= s_njob[l]) { jj -= s_njob[l]; ++l; }
-              const int slot2 = (int)jobq[l * kThreads + (int)jj];
-              const LightRec light = load_light(s, l);
-              const float4 h0 = h_p[slot2], h1 = h_n[slot2];
-              const float nr = q_tp[slot2].w;
-              f3 lightDir; float lightDistance, attenuation;
-              wf_light_vector(light, xyz(h0), lightDir, lightDistance, attenuation);
-              const f3 shadow_origin = smad3(xyz(h1), 0.001f, xyz(h0));          // glsl:381, :412 (P + N * 0.001)
-              const float sf = shadow_packets<BIG, FAN>(s, cand_base, nr, shadow_origin, light, l, lightDir, lightDistance);
+#if RT_RG_SPLIT
+            bool surv = false;
+            Cands cd; cd.base = cand_base; cd.n = 0; cd.first = 0; cd.nsph = 0; cd.list = true; cd.prefilter = false;
+            if (j < total) {                             // ---- B1
+              int l, slot2; LightRec light; float nr, lightDistance; f3 origin, lightDir;
+              job_of(j, l, slot2, light, nr, origin, lightDir, lightDistance);
+              bool done = false;
+              const float sf = shadow_packets_m<BIG, FAN, 1>(s, cand_base, nr, origin, light, l, lightDir, lightDistance, cd, done);
+              if (done) reinterpret_cast<float*>(brdf)[(l * kThreads + slot2) * 4 + 3] = sf;
+              else surv = true;
+            }
+            const unsigned sm = __ballot_sync(0xffffffffu, surv);
+            if (lane == 0) s_wsurv[warp] = (unsigned)__popc(sm);
+            __syncthreads();
+            unsigned before = 0, n_surv = 0;
+#pragma unroll
+            for (int w2 = 0; w2 < kWarpsPerCta; ++w2) { const unsigned c = s_wsurv[w2]; n_surv += c; if (w2 < warp) before += c; }
+            if (surv) {                                  // record: job | owner lane | list kind, candidate counts
+              const unsigned k = before + (unsigned)__popc(sm & lt);
+              surv_rec[k] = make_uint2(j | ((unsigned)tid << 16) | (cd.list ? 1u << 24 : 0u) | (cd.prefilter ? 1u << 25 : 0u),
+                                       (unsigned)cd.n | ((unsigned)cd.nsph << 16));
+            }
+            __syncthreads();
+            if ((unsigned)tid < n_surv) {                // ---- B2
+              const uint2 rec = surv_rec[tid];
+              int l, slot2; LightRec light; float nr, lightDistance; f3 origin, lightDir;
+              job_of(rec.x & 0xffffu, l, slot2, light, nr, origin, lightDir, lightDistance);
+              Cands cd2;
+              cd2.base = cand_base - (unsigned)tid * 2u + ((rec.x >> 16) & 0xffu) * 2u;     // the owner lane's scratch list
+              cd2.n = (int)(rec.y & 0xffffu); cd2.nsph = (int)(rec.y >> 16); cd2.first = 0;
+              cd2.list = (rec.x >> 24) & 1u; cd2.prefilter = (rec.x >> 25) & 1u;
+              bool done = false;
+              const float sf = shadow_packets_m<BIG, FAN, 2>(s, cand_base, nr, origin, light, l, lightDir, lightDistance, cd2, done);
               reinterpret_cast<float*>(brdf)[(l * kThreads + slot2) * 4 + 3] = sf;
             }
+            __syncthreads();                             // the candidate lists are free for the next batch
+#else
+            const bool full_warp = j0 + (unsigned)(warp * 32 + 32) <= total;    // warp-uniform: all 32 lanes hold a job
+            if (j < total) {
+              int l, slot2; LightRec light; float nr, lightDistance; f3 origin, lightDir;
+              job_of(j, l, slot2, light, nr, origin, lightDir, lightDistance);
+              const float sf = shadow_packets<BIG, FAN>(s, cand_base, nr, origin, light, l, lightDir, lightDistance, full_warp);
+              reinterpret_cast<float*>(brdf)[(l * kThreads + slot2) * 4 + 3] = sf;
+            }
+#endif
           }
         }
         __syncthreads();
@@ -311,7 +367,7 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
 
 template <bool BIG, bool BANDS, bool FAN>
 inline cudaError_t launch_regroup_t(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
-  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2 + regroup_queue_bytes(kp.sc.num_lights);
+  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kScratchBytes + regroup_queue_bytes(kp.sc.num_lights);
   int per_sm = 0;
   cudaError_t e = cached_occupancy(rt_regroup_kernel<BIG, BANDS, FAN>, kThreads, smem, &per_sm);
   if (e != cudaSuccess) return e;

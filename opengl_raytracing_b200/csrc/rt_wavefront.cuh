@@ -33,6 +33,9 @@ namespace pk {
 #endif
 // large scenes: 2 (128 registers). Measured on B200 (ms, 3 / 2 / 4 CTAs): C3 13.40 / 13.21 / 14.25, C5 7.73 / 7.54 / 7.85;
 // small scenes do not care (C2 0.4927 / 0.4907 / 0.5151). The bounce kernel stays at 3 (2: C3 14.13, C5 7.73).
+#ifndef RT_WF_SHADOW_COOP
+#define RT_WF_SHADOW_COOP 0
+#endif
 #ifndef RT_WF_SHADOW_MINB_BIG
 #define RT_WF_SHADOW_MINB_BIG 2
 #endif
@@ -41,6 +44,9 @@ namespace pk {
 template <bool BIG>
 __device__ __forceinline__ void wf_stage_scene(const KernelParams& kp, float4* smem, Scene& s, saddr& cand_base, Textures& tx) {
   const DeviceScene& sc = kp.sc;
+#if RT_PK_STATS
+  g_stats = kp.counters;
+#endif
   for (int i = threadIdx.x; i < sc.pk_float4s; i += kThreads) smem[i] = __ldg(sc.pk_blob + i);
   __syncthreads();
   const saddr base = (saddr)__cvta_generic_to_shared(smem);
@@ -55,6 +61,7 @@ __device__ __forceinline__ void wf_stage_scene(const KernelParams& kp, float4* s
   s.maxd = kp.fp.max_ray_distance;
   s.grid = BIG ? sc.pk_grid : nullptr; s.grid_off_f4 = sc.pk_grid_off_f4; s.grid_ent_f4 = sc.pk_grid_ent_f4;
   cand_base = base + (unsigned)sc.pk_float4s * 16u + threadIdx.x * 2u;
+  s.wlist = base + (unsigned)sc.pk_float4s * 16u + (unsigned)(kCandCap * kThreads * 2) + (threadIdx.x >> 5) * (unsigned)kWarpListBytes;
   tx.sky = sc.sky; tx.sky_tex = sc.sky_tex; tx.sky_size = sc.sky_size;
   tx.sky_hw = (kp.fp.flags & RT_FLAG_SKYBOX_HW) != 0u && sc.sky_tex != 0ull;
   tx.noise = sc.noise; tx.noise_w = sc.noise_w; tx.noise_h = sc.noise_h;
@@ -347,6 +354,10 @@ wf_shadow_kernel(const __grid_constant__ KernelParams kp, const __grid_constant_
       base = __shfl_sync(0xffffffffu, base, 0);
       if (base >= n) break;
       const unsigned j = base + (unsigned)lane;
+      // warp-uniform: all 32 lanes hold a job of light l. The shared prescan is OFF here by default: the job queue is filled
+      // by whole warps in arrival order, a warp's 32 jobs come from unrelated pixel blocks more often than in the regrouping
+      // megakernel (14 % of the scans found no common cone, 7 % overflowed) and C3 measured 13.3 -> 14.3 ms with it on.
+      const bool full_warp = RT_WF_SHADOW_COOP && base + 32u <= n;
       if (j >= n) continue;
       const unsigned slot = wp.jobq[(size_t)l * cap + j];
       const float4 h0 = hq[slot], h1 = hq[cap + slot];
@@ -355,7 +366,7 @@ wf_shadow_kernel(const __grid_constant__ KernelParams kp, const __grid_constant_
       f3 lightDir; float lightDistance, attenuation;
       wf_light_vector(light, P, lightDir, lightDistance, attenuation);
       const f3 shadow_origin = smad3(N, 0.001f, P);          // glsl:381, :412 (P + N * 0.001)
-      const float sf = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, l, lightDir, lightDistance);
+      const float sf = shadow_packets<BIG, FAN>(s, cand_base, noise_r, shadow_origin, light, l, lightDir, lightDistance, full_warp);
       sf_out[((size_t)l * cap + slot) * 4u + 3u] = sf;
     }
   }
@@ -363,7 +374,7 @@ wf_shadow_kernel(const __grid_constant__ KernelParams kp, const __grid_constant_
 
 template <typename K>
 inline cudaError_t wf_launch(K kernel, const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream) {
-  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kCandCap * kThreads * 2;
+  const size_t smem = (size_t)kp.sc.pk_float4s * sizeof(float4) + (size_t)kScratchBytes;
   int per_sm = 0;
   cudaError_t e = cached_occupancy(kernel, kThreads, smem, &per_sm);
   if (e != cudaSuccess) return e;
