@@ -67,10 +67,13 @@ def parse_args():
     ap.add_argument("--gather", choices=["peer", "nccl"], default="peer",
                     help="--shard rows: peer = interleaved bands stored straight into rank 0's frame over NVLink (CUDA IPC); "
                          "nccl = contiguous tiles gathered point to point")
-    ap.add_argument("--reduce", choices=["peer", "nccl"], default="nccl",
-                    help="--shard samples: nccl = dist.reduce (default: measured faster on this box, N=8 71 us vs 110 us for a 1080p frame: "
-                         "NVSwitch reduces in the fabric, the peer kernel makes rank 0 pull 7/8 of a frame AND receive 7/8 of the result); "
-                         "peer = the library's deterministic pull-reduce kernel over CUDA-IPC-mapped partial frames (rt_peer_reduce)")
+    ap.add_argument("--reduce", choices=["peer", "nccl"], default="peer",
+                    help="--shard samples: peer (default) = the library's deterministic pull-reduce kernel over CUDA-IPC-mapped partial "
+                         "frames (rt_peer_reduce), pipelined one frame deep: it runs on its own stream in CTA slots the render grid leaves "
+                         "free (rt_set_sm_reserve) while the NEXT frame renders; nccl = dist.reduce after each render on the same stream "
+                         "(alone it is the faster reduce, N=8 71 us vs 110 us for a 1080p frame, but an NCCL CTA needs a whole free SM)")
+    ap.add_argument("--pipeline", type=int, default=1, help="--reduce peer: 1 = overlap the reduce of frame i-1 with the render of frame i")
+    ap.add_argument("--sm-reserve", type=int, default=8, help="pipelined peer reduce: SMs' worth of CTA slots the render grid leaves free")
     ap.add_argument("--no-subrecords", action="store_true", help="N > 1: skip the c4_samples / c5_rows sub-records")
     ap.add_argument("--flags", type=lambda s: int(s, 0), default=0, help="extra RT_FLAG_* bits (e.g. 0x2 parity math)")
     ap.add_argument("--host-path", type=int, default=0, help="rt_set_host_path: 0 auto, 1 staged, 2 banded, 3 zero-copy")
@@ -322,6 +325,9 @@ def run_ours(args) -> None:
         params = workload_params(w, flags=flags | abi.FLAG_SUM_SAMPLES, frame_count=w.frame_count + rank * ns)
         scaling, par = "weak", (f"sample ranges x{world} ({ns} spp per rank), partial sums reduced to rank 0 "
                                 f"({'peer pull-reduce kernel over CUDA IPC' if args.reduce == 'peer' else 'NCCL reduce'})")
+        if args.reduce == "peer" and args.pipeline:
+            par += (f"; pipelined one frame deep: the reduce of frame i-1 runs on a second stream, in the CTA slots of {args.sm_reserve} SMs the "
+                    "render grid leaves free, inside the timed region of frame i (K timed regions = K renders + K reduces; three rotating partials)")
     else:
         params = workload_params(w, flags=flags)
         scaling, par = "weak", "single GPU"
@@ -334,7 +340,10 @@ def run_ours(args) -> None:
     reducer = None
     if world > 1 and args.shard == "samples" and args.reduce == "peer":
         reducer = sharding.PeerReducer(ctx, H, W)      # partial frames of every rank mapped into every rank (CUDA IPC)
-        color = reducer.partial                         # this rank renders its partial sum into its exported buffer
+        color = reducer.partial                         # (the counter pass; every frame renders into reducer.partial of ITS epoch)
+    pipelined = bool(reducer and args.pipeline)
+    if pipelined:
+        ctx.set_sm_reserve(args.sm_reserve)
 
     # ---- reference-literal op counts for THIS rank's work (untimed, counter variant)
     pc = abi.FrameParams.from_buffer_copy(params)
@@ -348,6 +357,9 @@ def run_ours(args) -> None:
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)   # > 126 MB L2
 
     out = (peer.color, peer.position, peer.normal) if peer else (color, position if write_geom else None, normal if write_geom else None)
+
+    def target():                                      # this frame's images: the peer reducer rotates its partial buffers by epoch
+        return (reducer.partial, out[1], out[2]) if reducer else out
 
     def collective():
         if peer:
@@ -363,8 +375,55 @@ def run_ours(args) -> None:
     def step():
         if params.flags & abi.FLAG_ACCUMULATE:
             color.zero_()
-        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
+        o = target()
+        ctx.render(params, o[0], o[1], o[2], None, stream.cuda_stream)
         collective()
+
+    class ReducePipeline:
+        """Frame i renders on `stream` while the peer reduce of frame i-1 runs on `side`. The reduce is enqueued behind
+        the START event of frame i's timed region (never inside the untimed L2 flush), and the region ends only when
+        both the render and that reduce are done: region i = max(render i, reduce i-1) + what they cost each other.
+        The render of frame i is ordered behind this rank's reduce of frame i-2 (sharding.PeerReducer: three partials)."""
+
+        def __init__(self):
+            self.side = torch.cuda.Stream(dev)
+            self.pending = None                        # render-done event of the frame whose reduce has not been enqueued
+            self.red_done = []
+
+        def _reduce_pending(self, after):
+            self.side.wait_event(after)
+            self.side.wait_event(self.pending)
+            reducer.reduce(self.side.cuda_stream, ns * world)
+            e = torch.cuda.Event(); e.record(self.side)
+            self.red_done = self.red_done[-1:] + [e]
+            self.pending = None
+
+        def frame(self, events=None, do_flush=False):
+            if do_flush:
+                flush.zero_()
+            a, b, c = events if events else (torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event())
+            a.record(stream)
+            had = self.pending is not None
+            if had:
+                self._reduce_pending(a)
+            if len(self.red_done) >= 2 or (self.red_done and not had):
+                stream.wait_event(self.red_done[0] if len(self.red_done) >= 2 else self.red_done[-1])
+            o = target()
+            ctx.render(params, o[0], o[1], o[2], None, stream.cuda_stream)
+            b.record(stream)
+            self.pending = b
+            if had:
+                stream.wait_event(self.red_done[-1])
+            c.record(stream)
+
+        def drain(self):
+            if self.pending is not None:
+                a = torch.cuda.Event(); a.record(stream)
+                self._reduce_pending(a)
+            if self.red_done:
+                stream.wait_event(self.red_done[-1])
+
+    pipe = ReducePipeline() if pipelined else None
 
     # ---- the variant is chosen ONCE, explicitly (rt_tune: every applicable variant timed on this scene and
     # frame shape, identical images), so that no warm-up or timed frame is a trial frame of the autotuner
@@ -372,7 +431,7 @@ def run_ours(args) -> None:
     tuning = ctx.tune(params)
     nwarm = max(3, args.warmup)
     for _ in range(nwarm):
-        step()
+        pipe.frame() if pipe else step()
     torch.cuda.synchronize(dev)
     fp32_peak = ctx.measure_fp32_peak()
     launches0 = ctx.launch_count()
@@ -386,15 +445,23 @@ def run_ours(args) -> None:
     sampler.start()
     t_wall0 = time.perf_counter()
     for i in range(args.steps):
+        if pipe:
+            pipe.frame(ev[i], do_flush=True)
+            continue
         flush.zero_()                                  # L2 flush between timed iterations (untimed)
         ev[i][0].record(stream)
         if params.flags & abi.FLAG_ACCUMULATE:
             color.zero_()
-        ctx.render(params, out[0], out[1], out[2], None, stream.cuda_stream)
+        o = target()
+        ctx.render(params, o[0], o[1], o[2], None, stream.cuda_stream)
         ev[i][1].record(stream)
         collective()
         ev[i][2].record(stream)
+    if pipe:
+        pipe.drain()                                   # the last frame's reduce (its twin, the last warm-up frame's, ran in region 0)
     torch.cuda.synchronize(dev)
+    if reducer:
+        reducer.check()
     if world > 1:
         dist.barrier()
     t_wall = time.perf_counter() - t_wall0
@@ -412,7 +479,7 @@ def run_ours(args) -> None:
         rays_total, flops_total = float(rays_rank), float(flops_rank)
     value = rays_total / (step_ms * 1e-3) / 1e6
 
-    sustained = sustained_leg(ctx, params, out, stream, dev, kern_ms, local) if rank == 0 or world > 1 else None
+    sustained = sustained_leg(ctx, params, target(), stream, dev, kern_ms, local) if rank == 0 or world > 1 else None
     if world > 1:
         dist.barrier()
 
@@ -599,12 +666,13 @@ def multi_gpu_subrecords(args, rank: int, world: int, local: int) -> dict:
     first, count = sharding.sample_range(S, rank, world)
     use_peer = args.reduce == "peer"
     reducer = sharding.PeerReducer(ctx, H, W) if use_peer else None
-    part = reducer.partial if reducer else torch.zeros(H, W, 4, device=dev)
+    part0 = None if reducer else torch.zeros(H, W, 4, device=dev)
     pos = torch.zeros(H, W, 4, device=dev) if rank == 0 else None
     nrm = torch.zeros(H, W, 4, dtype=torch.float16, device=dev) if rank == 0 else None
     p = workload_params(w, flags=abi.FLAG_SUM_SAMPLES, frame_count=w.frame_count + first, num_samples=max(count, 1))
 
     def c4_step():
+        part = reducer.partial if reducer else part0   # the reducer rotates its partial buffers by epoch
         if count > 0:
             ctx.render(p, part, pos, nrm, None, stream.cuda_stream)
         else:
@@ -625,7 +693,7 @@ def multi_gpu_subrecords(args, rank: int, world: int, local: int) -> dict:
                          "variant": var}
     if reducer:
         torch.cuda.synchronize(dev); dist.barrier(); reducer.close()
-    del part, full
+    del part0, full
     ctx.close()
 
     # ---- C5: interleaved row bands, fused peer stores

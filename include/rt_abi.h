@@ -336,6 +336,11 @@ rt_status rt_set_tuning(rt_context* ctx, const rt_tuning* tuning);
 /* on = 0: rt_render never times variants on the caller's launches (untuned shapes run the default
  * variant until rt_tune is called). Default: on.                                                */
 rt_status rt_set_autotune(rt_context* ctx, int on);
+/* Sizes every later render grid for (SM count - sms) multiprocessors, so that a kernel of another stream — the
+ * peer reduce of the previous frame (rt_multi.h), a post-processing chain — finds free CTA slots while a
+ * persistent render kernel is running instead of waiting for its last CTA. 0 (default) = the whole device;
+ * sms must be in [0, SM count). No counterpart in the reference (one GL queue, one dispatch at a time). */
+rt_status rt_set_sm_reserve(rt_context* ctx, int sms);
 
 /* Introspection of the host-side scene staging (no CUDA call, no context): builds the light grids
  * rt_upload_scene would build for these records (large scenes only) into

@@ -82,9 +82,13 @@ typedef struct rt_peer_reduce_desc {
 /* Enqueues ONE kernel on `cuda_stream` that (1) tells every peer that this rank's partial of `epoch` is complete
  * (everything enqueued on the stream before the call), (2) waits until every peer said so, (3) sums slice `rank`
  * of all partials in rank order, scales, and stores RGB + alpha 1 into `result`, (4) tells rank 0 the slice is
- * there; on rank 0 the kernel ends only when every slice is. Callers alternate two partial buffers between
- * consecutive epochs (a rank may render epoch e+1 while a peer still reads its partial of epoch e). Waits are
- * bounded (about 10 s): a peer that never arrives sets the status word and rt_peer_reduce_status reports it. */
+ * there; on rank 0 the kernel ends only when every slice is. Callers rotate the partial buffers between
+ * consecutive epochs (a rank may render epoch e+1 while a peer still reads its partial of epoch e): TWO when the
+ * render and the reduce share a stream; THREE when the reduce of epoch e runs on its own stream beside the render
+ * of epoch e+1 (rt_set_sm_reserve leaves it CTA slots) — then order the render of epoch e+2 behind this rank's
+ * reduce of epoch e: that kernel got past step (2) only after every peer had finished its reduce of epoch e-1,
+ * the last reader of the buffer epoch e+2 overwrites. Waits are bounded (about 10 s): a peer that never arrives
+ * sets the status word and rt_peer_reduce_status reports it. */
 rt_status rt_peer_reduce(rt_context* ctx, const rt_peer_reduce_desc* desc, void* cuda_stream);
 /* After synchronising: RT_OK, or RT_ERR_UNAVAILABLE when a wait of an earlier reduce timed out. own_flags = this rank's block. */
 rt_status rt_peer_reduce_status(rt_context* ctx, const uint32_t* own_flags);

@@ -35,7 +35,7 @@ EXPORTED_SYMBOLS = [
     "rt_set_skybox", "rt_set_noise", "rt_render", "rt_render_host", "rt_synchronize", "rt_render_gl",
     "rt_get_counters", "rt_set_host_path", "rt_device_alloc", "rt_device_free", "rt_ipc_export",
     "rt_ipc_open", "rt_ipc_close", "rt_host_alloc", "rt_host_free", "rt_measure_fp32_peak", "rt_launch_count",
-    "rt_debug_light_grids", "rt_render_static", "rt_tune", "rt_get_tuning", "rt_set_tuning", "rt_set_autotune",
+    "rt_debug_light_grids", "rt_render_static", "rt_tune", "rt_get_tuning", "rt_set_tuning", "rt_set_autotune", "rt_set_sm_reserve",
 ]
 KERNEL_AUTO, KERNEL_MEGAKERNEL, KERNEL_WAVEFRONT, KERNEL_LITERAL, KERNEL_REGROUP = -1, 0, 1, 2, 3
 TUNING_DEFAULT, TUNING_TRIALS, TUNING_CHOSEN, TUNING_PINNED = range(4)
@@ -178,6 +178,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_get_tuning.argtypes = [vp, C.POINTER(FrameParams), C.POINTER(Tuning)]
     lib.rt_set_tuning.argtypes = [vp, C.POINTER(Tuning)]
     lib.rt_set_autotune.argtypes = [vp, ip]
+    lib.rt_set_sm_reserve.argtypes = [vp, ip]
     # include/rt_post.h
     pp = C.POINTER(PostParams)
     lib.rt_generate_aabbs.argtypes = [vp, vp, ip]

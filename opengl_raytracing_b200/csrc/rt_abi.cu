@@ -30,6 +30,7 @@ static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBy
 struct rt_context {
   int device = 0;
   int sm_count = 0;
+  int sm_reserve = 0;            // rt_set_sm_reserve: render grids are sized for sm_count - sm_reserve SMs
   int max_smem_optin = 0;
   std::string err;
   // scene blob (device) + pinned staging (host)
@@ -924,11 +925,11 @@ static rt_status wavefront_render(rt_context* c, LaunchPlan& L, cudaStream_t str
       RT_CUDA(c, cudaMemsetAsync(wp.counters, 0, rt::kWfCounters * sizeof(unsigned), stream));
       for (int d = 0; d <= D; ++d) {
         wp.depth = d;
-        cudaError_t e = L.par ? rt::launch_wf_bounce_parity(kp, wp, c->sm_count, stream) : rt::launch_wf_bounce_fast(kp, wp, c->sm_count, stream);
+        cudaError_t e = L.par ? rt::launch_wf_bounce_parity(kp, wp, c->sm_count - c->sm_reserve, stream) : rt::launch_wf_bounce_fast(kp, wp, c->sm_count - c->sm_reserve, stream);
         if (e != cudaSuccess) return cuda_fail(c, e, "wavefront bounce launch");
         c->launches += 1;
         if (d == D || nl == 0) continue;
-        e = L.par ? rt::launch_wf_shadow_parity(kp, wp, c->sm_count, stream) : rt::launch_wf_shadow_fast(kp, wp, c->sm_count, stream);
+        e = L.par ? rt::launch_wf_shadow_parity(kp, wp, c->sm_count - c->sm_reserve, stream) : rt::launch_wf_shadow_fast(kp, wp, c->sm_count - c->sm_reserve, stream);
         if (e != cudaSuccess) return cuda_fail(c, e, "wavefront shadow launch");
         c->launches += 1;
       }
@@ -956,13 +957,13 @@ static rt_status launch_variant(rt_context* c, LaunchPlan& L, rt_context::Varian
   unsigned advance = 0;
   cudaError_t e;
   if (L.use_packet && v.kernel == RT_KERNEL_REGROUP) {
-    e = L.par ? rt::launch_regroup_parity(kp, c->sm_count, stream, &advance) : rt::launch_regroup_fast(kp, c->sm_count, stream, &advance);
+    e = L.par ? rt::launch_regroup_parity(kp, c->sm_count - c->sm_reserve, stream, &advance) : rt::launch_regroup_fast(kp, c->sm_count - c->sm_reserve, stream, &advance);
     c->launches += 1;
   } else if (L.use_packet) {
-    e = L.par ? rt::launch_packet_parity(kp, c->sm_count, stream, &advance) : rt::launch_packet_fast(kp, c->sm_count, stream, &advance);
+    e = L.par ? rt::launch_packet_parity(kp, c->sm_count - c->sm_reserve, stream, &advance) : rt::launch_packet_fast(kp, c->sm_count - c->sm_reserve, stream, &advance);
     c->launches += 1;
   } else {
-    e = L.par ? rt::launch_render_parity(kp, c->sm_count, stream, &advance) : rt::launch_render_fast(kp, c->sm_count, stream, &advance);
+    e = L.par ? rt::launch_render_parity(kp, c->sm_count - c->sm_reserve, stream, &advance) : rt::launch_render_fast(kp, c->sm_count - c->sm_reserve, stream, &advance);
     c->launches += 1;
   }
   if (e != cudaSuccess) return cuda_fail(c, e, "rt_render launch");
@@ -1116,6 +1117,13 @@ rt_status rt_set_tuning(rt_context* c, const rt_tuning* tuning) {
     return fail(c, RT_ERR_INVALID_ARG, "rt_set_tuning: kernel / registers / phase_level out of range");
   c->pinned = true;
   c->pin = {tuning->kernel, tuning->registers, tuning->phase_level};
+  return RT_OK;
+}
+
+rt_status rt_set_sm_reserve(rt_context* c, int sms) {
+  if (!c) return RT_ERR_INVALID_ARG;
+  if (sms < 0 || sms >= c->sm_count) return fail(c, RT_ERR_INVALID_ARG, "rt_set_sm_reserve: sms must be in [0, SM count)");
+  c->sm_reserve = sms;
   return RT_OK;
 }
 

@@ -146,6 +146,10 @@ class RtContext:
     def set_autotune(self, on: bool) -> None:
         self._check(self.lib.rt_set_autotune(self.handle, 1 if on else 0))
 
+    def set_sm_reserve(self, sms: int) -> None:
+        """Render grids are sized for (SM count - sms) SMs: room for a kernel of another stream (rt_set_sm_reserve)."""
+        self._check(self.lib.rt_set_sm_reserve(self.handle, int(sms)))
+
 
 def frame_params(width: int, height: int, num_objects: int, num_lights: int, camera: S.Camera | None = None,
                  max_ray_depth: int = 3, frame_count: int = 0, num_samples: int = 1, use_skybox: bool = False,

@@ -149,9 +149,17 @@ class PeerReducer:
     result frame and a block of flag words per rank are CUDA-IPC mapped into every rank; ``reduce`` enqueues ONE
     kernel (rt_peer_reduce, include/rt_multi.h) that signals "my partial is complete", waits for every peer, sums
     this rank's slice of all partials in rank order (deterministic), scales, and stores it into rank 0's frame.
-    Two partial buffers alternate between consecutive reduces (a rank may render the next frame while a peer
-    still reads its partial of this one): render into ``partial`` (the buffer of the NEXT reduce), then call
-    ``reduce``. ``result`` on rank 0 = the finished mean frame."""
+    THREE partial buffers rotate between consecutive reduces: render into ``partial`` (the buffer of the NEXT
+    reduce), then call ``reduce``. ``result`` on rank 0 = the finished mean frame.
+
+    Why three: a reduce kernel passes its entry wait only once every peer has STARTED the reduce of the same epoch,
+    i.e. (stream order on the peer) finished the one before. So when this rank's reduce of epoch j has completed,
+    every peer is done reading this rank's partial of epoch j-1 — the buffer the render of epoch j+2 writes. The
+    caller may therefore overlap the reduce of frame j with the render of frame j+1 on another stream (bench.py's
+    pipelined mode), as long as the render of frame j+2 is ordered behind this rank's reduce of frame j (an event).
+    With the render and the reduce on ONE stream two buffers would do; the third is what makes the overlap safe."""
+
+    NBUF = 3
 
     FLAG_BYTES = 2 << 20          # its own 2 MB allocation: CUDA IPC handles map whole allocations
 
@@ -165,8 +173,8 @@ class PeerReducer:
         assert self.world <= abi.RT_MAX_PEERS
         self.epoch = 0
         nbytes = height * width * 16
-        names = ["partial0", "partial1", "flags"] + (["result"] if self.rank == 0 else [])
-        self.own, handles = {}, torch.zeros(4, 64, dtype=torch.uint8)
+        names = ["partial%d" % i for i in range(self.NBUF)] + ["flags"] + (["result"] if self.rank == 0 else [])
+        self.own, handles = {}, torch.zeros(self.NBUF + 2, 64, dtype=torch.uint8)
         for i, name in enumerate(names):
             p = C.c_void_p(0)
             ctx._check(ctx.lib.rt_device_alloc(ctx.handle, C.byref(p), self.FLAG_BYTES if name == "flags" else nbytes))
@@ -190,7 +198,7 @@ class PeerReducer:
                 continue
             hb = everyone[r].cpu().numpy()
             m = {}
-            for i, name in enumerate(["partial0", "partial1", "flags"] + (["result"] if r == 0 else [])):
+            for i, name in enumerate(["partial%d" % k for k in range(self.NBUF)] + ["flags"] + (["result"] if r == 0 else [])):
                 p = C.c_void_p(0)
                 ctx._check(ctx.lib.rt_ipc_open(ctx.handle, hb[i].tobytes(), C.byref(p)))
                 m[name] = p.value
@@ -205,7 +213,7 @@ class PeerReducer:
     @property
     def partial(self):
         """The buffer this rank renders its partial sum of the NEXT reduce into (a torch view)."""
-        return self._tensor(self.own["partial%d" % ((self.epoch + 1) & 1)])
+        return self._tensor(self.own["partial%d" % ((self.epoch + 1) % self.NBUF)])
 
     @property
     def result(self):
@@ -219,7 +227,7 @@ class PeerReducer:
         d = abi.PeerReduceDesc()
         d.rank, d.world = self.rank, self.world
         for r in range(self.world):
-            d.partial[r] = self.maps[r]["partial%d" % (self.epoch & 1)]
+            d.partial[r] = self.maps[r]["partial%d" % (self.epoch % self.NBUF)]
             d.flags[r] = self.maps[r]["flags"]
         d.result = self.maps[0]["result"]
         d.pixels, d.scale, d.epoch = self.h * self.w, 1.0 / float(total_samples), self.epoch

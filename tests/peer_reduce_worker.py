@@ -45,6 +45,46 @@ def main():
             print(f"frame {frame}: max |mean - one-GPU mean| = {err:.3g} {'ok' if good else 'MISMATCH'}", flush=True)
             ok = ok and good
         dist.barrier()
+    # ---- pipelined: the reduce of frame i-1 on a second stream beside the render of frame i (three rotating partials,
+    # the render of frame i ordered behind this rank's reduce of frame i-2), every frame different
+    ctx.set_sm_reserve(4)
+    main, side = torch.cuda.current_stream(), torch.cuda.Stream()
+    frames, results, red_done, pending = 6, [], [], None
+    for frame in range(frames + 1):
+        if pending is not None:
+            side.wait_event(pending)
+            red.reduce(side.cuda_stream, w.num_samples)
+            if rank == 0:
+                with torch.cuda.stream(side):
+                    results.append(red.result.clone())
+            e = torch.cuda.Event(); e.record(side); red_done.append(e)
+            pending = None
+        if frame == frames:
+            break
+        if len(red_done) >= 2:
+            main.wait_event(red_done[-2])
+        fc = w.frame_count + 7 * (frame + 1)
+        p = workload_params(w, flags=abi.FLAG_SUM_SAMPLES, frame_count=fc + first, num_samples=count)
+        ctx.render(p, red.partial, None, None, None, main.cuda_stream)
+        pending = torch.cuda.Event(); pending.record(main)
+    torch.cuda.synchronize()
+    red.check()
+    dist.barrier()
+    ctx.set_sm_reserve(0)
+    if rank == 0:
+        base = w.frame_count
+        for frame, got_t in enumerate(results):
+            w.frame_count = base + 7 * (frame + 1)
+            full = render_workload(ctx, w, bind=False)["color"]
+            got = got_t.cpu().numpy()
+            fin = np.isfinite(full).all(axis=-1)
+            err = float(np.abs(got[fin] - full[fin]).max())
+            good = err <= 2e-5 * max(1.0, float(np.abs(full[fin]).max())) and bool((got[..., 3] == 1.0).all())
+            print(f"pipelined frame {frame}: max |mean - one-GPU mean| = {err:.3g} {'ok' if good else 'MISMATCH'}", flush=True)
+            ok = ok and good
+        w.frame_count = base
+        ok = ok and len(results) == frames
+    dist.barrier()
     if rank == 0:
         print("PEER_REDUCE_OK" if ok else "PEER_REDUCE_MISMATCH", flush=True)
     red.close()
