@@ -19,13 +19,17 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-ffp-contract=o
 UNITS = [  # (source, extra flags)
     ("rt_kernel_fast.cu", ["-fmad=false"]),
     ("rt_kernel_parity.cu", ["-fmad=false"]),
+    ("rt_regroup_fast_small.cu", ["-fmad=false"]),      # the regrouping megakernel: own units, own CTA sizes (rt_regroup_tu.inc)
+    ("rt_regroup_fast_big.cu", ["-fmad=false"]),
+    ("rt_regroup_parity_small.cu", ["-fmad=false"]),
+    ("rt_regroup_parity_big.cu", ["-fmad=false"]),
     ("rt_abi.cu", []),
     ("rt_post.cu", ["-fmad=false"]),
     ("rt_frame.cu", ["-fmad=false"]),
     ("rt_peak.cu", []),
     ("rt_multi.cu", []),
 ]
-HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_wavefront.cuh", "rt_regroup.cuh", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
+HEADERS = ["rt_kernel.cuh", "rt_packet.cuh", "rt_wavefront.cuh", "rt_regroup.cuh", "rt_regroup_tu.inc", "rt_math.cuh", "rt_device.h", os.path.join("..", "..", "include", "rt_abi.h"),
            os.path.join("..", "..", "include", "rt_post.h"), os.path.join("..", "..", "include", "rt_frame.h"),
            os.path.join("..", "..", "include", "rt_multi.h")]
 

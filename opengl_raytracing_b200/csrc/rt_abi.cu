@@ -586,6 +586,8 @@ rt_status rt_create(rt_context** out, int cuda_device) {
     for (int j = i; j > 0 && h3t[order[j]] < h3t[order[j - 1]]; --j) { int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t; }
   if ((e = rt::upload_tables_fast(h2, h3t, order)) != cudaSuccess) return bail(e);
   if ((e = rt::upload_tables_parity(h2, h3t, order)) != cudaSuccess) return bail(e);
+  if ((e = rt::upload_tables_fast_small(h2, h3t, order)) != cudaSuccess || (e = rt::upload_tables_fast_big(h2, h3t, order)) != cudaSuccess ||
+      (e = rt::upload_tables_parity_small(h2, h3t, order)) != cudaSuccess || (e = rt::upload_tables_parity_big(h2, h3t, order)) != cudaSuccess) return bail(e);
   if (const char* e2 = getenv("RT_PK_COHERENT")) c->coherent_override = atoi(e2);
   if (const char* e3 = getenv("RT_PK_DENSE")) c->dense_override = atoi(e3);
   if (const char* e4 = getenv("RT_PK_FAN")) c->fan_override = atoi(e4);
@@ -837,7 +839,7 @@ static rt_status plan_launch(rt_context* c, const rt_frame_params* p, LaunchPlan
         }
     }
     if (sc.num_lights <= rt::regroup_max_lights() && c->regroup_override != 0 &&
-        rt::regroup_smem_bytes((int)c->pk_float4s, sc.num_lights) <= (size_t)c->max_smem_optin - 1024) {
+        rt::regroup_smem_bytes((int)c->pk_float4s, sc.num_lights, sc.pk_big != 0) <= (size_t)c->max_smem_optin - 1024) {
       if (c->regroup_override == 1) L.nv = 0;              // RT_PK_REGROUP=1 pins it
       L.v[L.nv++] = {RT_KERNEL_REGROUP, 0, 0};
     }

@@ -145,10 +145,25 @@ struct WfParams {
 bool wavefront_supported(const KernelParams& kp);
 size_t packet_smem_bytes(int pk_float4s);   // dynamic shared memory of the packet / wavefront kernels for a blob of that size
 // the persistent megakernel with in-CTA ray regrouping (rt_regroup.cuh)
-size_t regroup_smem_bytes(int pk_float4s, int num_lights);
-int regroup_max_lights();
-cudaError_t launch_regroup_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance);
-cudaError_t launch_regroup_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance);
+// Four translation units (rt_regroup_{fast,parity}_{small,big}.cu, see rt_regroup_tu.inc): the small- and the large-scene
+// kernel run different CTA sizes, and each unit has its own copies of the __constant__ tables.
+constexpr int kRgMaxLights = 16;
+#define RT_RG_DECL(tu) \
+  cudaError_t launch_regroup_##tu(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance); \
+  size_t regroup_smem_bytes_##tu(int pk_float4s, int num_lights); \
+  cudaError_t upload_tables_##tu(const float* halton2, const float* halton3, const int* probe_order);
+RT_RG_DECL(fast_small) RT_RG_DECL(fast_big) RT_RG_DECL(parity_small) RT_RG_DECL(parity_big)
+#undef RT_RG_DECL
+inline size_t regroup_smem_bytes(int pk_float4s, int num_lights, bool big) {     // (the parity units use the same sizes)
+  return big ? regroup_smem_bytes_fast_big(pk_float4s, num_lights) : regroup_smem_bytes_fast_small(pk_float4s, num_lights);
+}
+inline int regroup_max_lights() { return kRgMaxLights; }
+inline cudaError_t launch_regroup_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
+  return kp.sc.pk_big ? launch_regroup_fast_big(kp, sm_count, stream, advance) : launch_regroup_fast_small(kp, sm_count, stream, advance);
+}
+inline cudaError_t launch_regroup_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
+  return kp.sc.pk_big ? launch_regroup_parity_big(kp, sm_count, stream, advance) : launch_regroup_parity_small(kp, sm_count, stream, advance);
+}
 cudaError_t launch_wf_bounce_fast(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
 cudaError_t launch_wf_bounce_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);
 cudaError_t launch_wf_shadow_fast(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream);

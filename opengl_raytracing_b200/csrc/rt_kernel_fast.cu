@@ -5,7 +5,6 @@
 #include "rt_kernel.cuh"
 #include "rt_packet.cuh"
 #include "rt_wavefront.cuh"
-#include "rt_regroup.cuh"
 
 namespace rt {
 cudaError_t launch_render_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
@@ -33,11 +32,4 @@ bool wavefront_supported(const KernelParams& kp) {
   return kp.sc.pk_float4s > 0 && kp.sc.num_lights <= kWfMaxLights && kp.fp.max_ray_depth <= kWfMaxDepth &&
          kp.fp.width <= 65535 && kp.fp.height <= 65535;
 }
-cudaError_t launch_regroup_fast(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
-  return fast::pk::launch_regroup(kp, sm_count, stream, advance);
-}
-size_t regroup_smem_bytes(int pk_float4s, int num_lights) {
-  return packet_smem_bytes(pk_float4s) + fast::pk::regroup_queue_bytes(num_lights);
-}
-int regroup_max_lights() { return fast::pk::kRgMaxLights; }
 }  // namespace rt

@@ -5,7 +5,6 @@
 #include "rt_kernel.cuh"
 #include "rt_packet.cuh"
 #include "rt_wavefront.cuh"
-#include "rt_regroup.cuh"
 
 namespace rt {
 cudaError_t launch_render_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* warps_launched) {
@@ -24,8 +23,5 @@ cudaError_t launch_wf_bounce_parity(const KernelParams& kp, const WfParams& wp, 
 }
 cudaError_t launch_wf_shadow_parity(const KernelParams& kp, const WfParams& wp, int sm_count, cudaStream_t stream) {
   return parity::pk::launch_wf_shadow(kp, wp, sm_count, stream);
-}
-cudaError_t launch_regroup_parity(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
-  return parity::pk::launch_regroup(kp, sm_count, stream, advance);
 }
 }  // namespace rt

@@ -36,15 +36,14 @@ namespace pk {
 #ifndef RT_RG_SPLIT
 #define RT_RG_SPLIT 0
 #endif
-constexpr int kRgMaxLights = 16;
 
 // bytes of dynamic shared memory behind the scene blob and the candidate scratch, for nl lights
 __host__ __device__ inline size_t regroup_queue_bytes(int nl) {
-  return (size_t)kThreads * (3 * 16 + 2 * 16 + 16 + 8) + (size_t)(nl > 0 ? nl : 1) * kThreads * (16 + 1);
+  return (size_t)kThreads * (3 * 16 + 2 * 16 + 16 + 8) + (size_t)(nl > 0 ? nl : 1) * kThreads * (16 + 2);
 }
 
 template <bool BIG, bool BANDS, bool FAN>
-__global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) * 8 / RT_PK_WARPS) rt_regroup_kernel(const __grid_constant__ KernelParams kp) {
+__global__ void __launch_bounds__(kThreads, ((BIG ? RT_RG_MINB_BIG : RT_RG_MINB) * 8 / RT_PK_WARPS > 0 ? (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) * 8 / RT_PK_WARPS : 1)) rt_regroup_kernel(const __grid_constant__ KernelParams kp) {
   extern __shared__ float4 smem[];
   const rt_frame_params& fp = kp.fp;
   Scene s; saddr cand_base; Textures tx;
@@ -60,8 +59,16 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
   float4* sum = q + 5 * kThreads;        // per pixel of the block: running colour sum over the samples
   uint2* surv_rec = reinterpret_cast<uint2*>(q + 6 * kThreads);   // round B: the surviving jobs of a batch (kThreads x 8 B = half a plane)
   float4* brdf = q + 6 * kThreads + kThreads / 2;                 // nl planes: (BRDF term, shadow factor)
-  unsigned char* jobq = reinterpret_cast<unsigned char*>(brdf + (size_t)(nl > 0 ? nl : 1) * kThreads);   // nl planes of hit slots
+  unsigned short* jobq = reinterpret_cast<unsigned short*>(brdf + (size_t)(nl > 0 ? nl : 1) * kThreads);   // nl planes of hit slots
   __shared__ unsigned s_tile, s_nhit, s_njob[kRgMaxLights], s_wsurv[kWarpsPerCta];
+  __shared__ unsigned s_jobcur;                       // round B: the next unclaimed batch of 32 jobs
+  __shared__ unsigned char s_lorder[kRgMaxLights];    // round B visits the lights in this order: the expensive ones (PCSS) first
+  if (threadIdx.x == 0) {
+    int k = 0;
+    for (int pass = 0; pass < 2; ++pass)
+      for (int l = 0; l < nl; ++l)
+        if ((load_light(s, l).shadowType == 2) == (pass == 0)) s_lorder[k++] = (unsigned char)l;
+  }
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned lt = (1u << lane) - 1u;
@@ -176,7 +183,7 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
             finish = true;
           }
         }
-        if (tid == 0) s_nhit = 0u;
+        if (tid == 0) { s_nhit = 0u; s_jobcur = 0u; }
         if (tid < kRgMaxLights) s_njob[tid] = 0u;
         __syncthreads();                                 // every parked record of the previous depth has been read
 
@@ -261,7 +268,7 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
               unsigned jb = 0;
               if (lane == 0) jb = atomicAdd(&s_njob[l], (unsigned)__popc(jm));
               jb = __shfl_sync(0xffffffffu, jb, 0);
-              if (job) jobq[l * kThreads + (int)(jb + (unsigned)__popc(jm & lt))] = (unsigned char)slot;
+              if (job) jobq[l * kThreads + (int)(jb + (unsigned)__popc(jm & lt))] = (unsigned short)slot;
             }
           }
         }
@@ -285,8 +292,9 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
           for (int l = 0; l < nl; ++l) total += s_njob[l];
           // the job of index j: (light, hit slot) and everything shadow_packets needs — recomputed in B2 from the same records
           auto job_of = [&](unsigned j, int& l, int& slot2, LightRec& light, float& nr, f3& origin, f3& lightDir, float& lightDistance) {
-            l = 0; unsigned jj = j;
-            while (jj >= s_njob[l]) { jj -= s_njob[l]; ++l; }
+            int li = 0; unsigned jj = j;
+            l = s_lorder[0];
+            while (jj >= s_njob[l]) { jj -= s_njob[l]; l = s_lorder[++li]; }
             slot2 = (int)jobq[l * kThreads + (int)jj];
             light = load_light(s, l);
             const float4 h0 = h_p[slot2], h1 = h_n[slot2];
@@ -295,10 +303,10 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
             wf_light_vector(light, xyz(h0), lightDir, lightDistance, attenuation);
             origin = smad3(xyz(h1), 0.001f, xyz(h0));                            // glsl:381, :412 (P + N * 0.001)
           };
+#if RT_RG_SPLIT
 #pragma unroll 1
           for (unsigned j0 = 0; j0 < total; j0 += kThreads) {
             const unsigned j = j0 + (unsigned)tid;
-#if RT_RG_SPLIT
             bool surv = false;
             Cands cd; cd.base = cand_base; cd.n = 0; cd.first = 0; cd.nsph = 0; cd.list = true; cd.prefilter = false;
             if (j < total) {                             // ---- B1
@@ -334,16 +342,27 @@ __global__ void __launch_bounds__(kThreads, (BIG ? RT_RG_MINB_BIG : RT_RG_MINB) 
               reinterpret_cast<float*>(brdf)[(l * kThreads + slot2) * 4 + 3] = sf;
             }
             __syncthreads();                             // the candidate lists are free for the next batch
+          }
 #else
-            const bool full_warp = j0 + (unsigned)(warp * 32 + 32) <= total;    // warp-uniform: all 32 lanes hold a job
+          // Batches of 32 consecutive jobs, claimed by whichever warp is free (one shared-memory atomic per batch): a warp
+          // that drew a batch of wide-cone jobs takes fewer batches, and the expensive lights go first, so the barrier
+          // behind the round waits for a short tail (ncu, C3 before: 17 % of all warp samples sat at that barrier).
+#pragma unroll 1
+          for (;;) {
+            unsigned j0 = 0;
+            if (lane == 0) j0 = atomicAdd(&s_jobcur, 32u);
+            j0 = __shfl_sync(0xffffffffu, j0, 0);
+            if (j0 >= total) break;
+            const unsigned j = j0 + (unsigned)lane;
+            const bool full_warp = j0 + 32u <= total;                           // warp-uniform: all 32 lanes hold a job
             if (j < total) {
               int l, slot2; LightRec light; float nr, lightDistance; f3 origin, lightDir;
               job_of(j, l, slot2, light, nr, origin, lightDir, lightDistance);
               const float sf = shadow_packets<BIG, FAN>(s, cand_base, nr, origin, light, l, lightDir, lightDistance, full_warp);
               reinterpret_cast<float*>(brdf)[(l * kThreads + slot2) * 4 + 3] = sf;
             }
-#endif
           }
+#endif
         }
         __syncthreads();
       }
@@ -382,8 +401,14 @@ inline cudaError_t launch_regroup_t(const KernelParams& kp, int sm_count, cudaSt
 
 template <bool BANDS, bool FAN>
 inline cudaError_t launch_regroup_f(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
+#if defined(RT_RG_ONLY_BIG) && RT_RG_ONLY_BIG == 1        // this translation unit holds the large-scene kernel only
+  return launch_regroup_t<true, BANDS, FAN>(kp, sm_count, stream, advance);
+#elif defined(RT_RG_ONLY_BIG)
+  return launch_regroup_t<false, BANDS, FAN>(kp, sm_count, stream, advance);
+#else
   return kp.sc.pk_big ? launch_regroup_t<true, BANDS, FAN>(kp, sm_count, stream, advance)
                       : launch_regroup_t<false, BANDS, FAN>(kp, sm_count, stream, advance);
+#endif
 }
 inline cudaError_t launch_regroup(const KernelParams& kp, int sm_count, cudaStream_t stream, unsigned* advance) {
 #if !RT_PARITY

@@ -80,6 +80,27 @@ def main():
     for f, a in sorted(agg.items(), key=lambda x: -x[1][0]):
         print(f"{f:24s} " + " ".join(f"{100 * a[j] / tot[j]:6.2f}" for j in range(len(names))) + f" {a[-1]:6d}")
     print("total samples", tot[0], "executed warp-inst", tot[1])
+    # the unattributed part ("?": kernel bodies, small helpers) by the source line of its OUTERMOST frame inside our headers,
+    # so that a whole inlined helper chain counts for the kernel-body line that called it
+    lines = {}
+    for i in range(n):
+        f = "?"
+        for fr in stacks[i]:
+            g = fn_of(fr)
+            if g in MAJOR: f = g; break
+        if f != "?": continue
+        key = None
+        for fr in reversed(stacks[i]):       # outermost first
+            if fr[0] in ranges: key = fr; break
+        if key is None and stacks[i]: key = stacks[i][-1]
+        a = lines.setdefault(key, [0] * (len(names) + 1))
+        for j, v in enumerate(prof[i]): a[j] += v
+        a[-1] += 1
+    top = int(os.environ.get("NCU_FUNCS_LINES", "60"))
+    print(f"-- unattributed code by source line (outermost frame), top {top} by samples")
+    for key, a in sorted(lines.items(), key=lambda x: -x[1][0])[:top]:
+        k = f"{key[0]}:{key[1]}" if key else "(no line info)"
+        print(f"{k:28s} " + " ".join(f"{100 * a[j] / tot[j]:6.2f}" for j in range(len(names))) + f" {a[-1]:6d}")
 
 
 if __name__ == "__main__":

@@ -3,7 +3,7 @@
 import re, subprocess, sys, os
 here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "opengl_raytracing_b200", "csrc")
 variant = sys.argv[1] if len(sys.argv) > 1 else ""
-for f in ("rt_kernel_fast", "rt_kernel_parity", "rt_post", "rt_multi"):
+for f in ("rt_kernel_fast", "rt_kernel_parity", "rt_regroup_fast_small", "rt_regroup_fast_big", "rt_regroup_parity_small", "rt_regroup_parity_big", "rt_post", "rt_multi"):
     path = os.path.join(here, f + variant + ".o.log")
     if not os.path.isfile(path):
         continue
@@ -14,5 +14,5 @@ for f in ("rt_kernel_fast", "rt_kernel_parity", "rt_post", "rt_multi"):
         ms = re.findall(r"(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads", body)
         stack, ss, sl = ms[-1] if ms else ("?", "?", "?")
         d = subprocess.run(["c++filt", name], capture_output=True, text=True).stdout.strip()
-        d = re.sub(r"\(.*", "", d).replace("rt::fast::", "").replace("rt::parity::", "").replace("void ", "")
+        d = re.sub(r"\(.*", "", d).replace("rt::fast::", "").replace("rt::parity::", "").replace("rt::fast_rg_small::", "").replace("rt::fast_rg_big::", "").replace("rt::parity_rg_small::", "").replace("rt::parity_rg_big::", "").replace("void ", "")
         print(f"  {d:58s} regs {regs:>3} stack {stack:>4} spill st {ss:>4} ld {sl:>4}")
