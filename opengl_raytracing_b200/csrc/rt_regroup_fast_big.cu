@@ -1,10 +1,10 @@
-// rt_regroup_fast_big.cu — the regrouping megakernel, fast math, big-scene kernel, 16 warps per CTA (see rt_regroup_tu.inc).
+// rt_regroup_fast_big.cu — the regrouping megakernel, fast math, big-scene kernel, 20 warps per CTA (see rt_regroup_tu.inc).
 #define RT_PARITY 0
 #define RT_VARIANT_NS fast_rg_big
 #define RT_RG_TU fast_big
 #define RT_RG_ONLY_BIG 1
 #ifndef RT_RG_WARPS_BIG
-#define RT_RG_WARPS_BIG 16
+#define RT_RG_WARPS_BIG 20
 #endif
 #undef RT_PK_WARPS
 #define RT_PK_WARPS RT_RG_WARPS_BIG
