@@ -202,3 +202,19 @@ def test_rt_tune_picks_a_variant_and_never_changes_the_image():
     for f in frames:
         assert _bits_equal(f, base) == ZERO
     c.close()
+
+
+def test_sm_reserve_shrinks_the_grid_not_the_image(rt_ctx):
+    """rt_set_sm_reserve: render grids sized for fewer SMs (room for a kernel of another stream); same bits, bad values rejected."""
+    w = synthetic.config(3, 480, 270)
+    base = render_workload(rt_ctx, w, flags=abi.FLAG_NORMAL_FP32)
+    try:
+        for sms in (8, 100, 147):
+            rt_ctx.set_sm_reserve(sms)
+            a, b = _both(rt_ctx, w, abi.FLAG_NORMAL_FP32, bind=False)
+            assert _bits_equal(base, a) == ZERO and _bits_equal(base, b) == ZERO, sms
+        for bad in (-1, 148, 10 ** 6):
+            with pytest.raises(Exception):
+                rt_ctx.set_sm_reserve(bad)
+    finally:
+        rt_ctx.set_sm_reserve(0)
