@@ -11,10 +11,14 @@ namespace rt {
 
 // Packet-kernel sphere clusters: every kPkClusterSize consecutive sphere slots share one
 // cluster record; built from kPkClusterMinSpheres spheres on (rt_abi.cu stage_scene_packet).
+// 8 since the warp-cooperative scan (rt_packet.cuh coop_cluster_scan): the warp shares the first level, so twice as many,
+// tighter clusters cost it two more steps and save every lane member tests (B200, regroup: C3 10.20 / 10.03 / 10.06 ms and
+// C5 4.68 / 4.55 / 6.76 ms at 16 / 8 / 4 spheres per cluster, shared sphere list 128; 32: 10.33 / 4.92). The per-lane walk
+// of round 1 preferred 16.
 #ifndef RT_PK_CLUSTER
-#define RT_PK_CLUSTER 16
+#define RT_PK_CLUSTER 8
 #endif
-constexpr int kPkClusterSize = RT_PK_CLUSTER;   // (dev A/B: -DRT_PK_CLUSTER=8)
+constexpr int kPkClusterSize = RT_PK_CLUSTER;
 constexpr int kPkClusterMinSpheres = 64;
 
 // Device-resident scene in the layout the kernel stages into shared memory. Built on the

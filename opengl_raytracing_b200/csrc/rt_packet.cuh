@@ -194,7 +194,7 @@ constexpr int kCandCap = 32;          // per-thread scratch list (u16 codes) in 
 #define RT_PK_WCLUSTERS 128
 #endif
 #ifndef RT_PK_WSPHERES
-#define RT_PK_WSPHERES 64
+#define RT_PK_WSPHERES 128
 #endif
 // per-warp lists of the cooperative cluster scan (coop_cluster_scan): passing clusters, then passing sphere slots (u16 each)
 constexpr int kWarpClusterCap = RT_PK_WCLUSTERS, kWarpSphereCap = RT_PK_WSPHERES;
