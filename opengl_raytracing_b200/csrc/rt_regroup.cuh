@@ -36,6 +36,7 @@ namespace pk {
 #ifndef RT_RG_SPLIT
 #define RT_RG_SPLIT 0
 #endif
+static_assert(!RT_RG_SPLIT || kThreads <= 256, "RT_RG_SPLIT packs the owner lane into 8 bits: build it with RT_RG_WARPS_SMALL=8 RT_RG_WARPS_BIG=8");
 
 // bytes of dynamic shared memory behind the scene blob and the candidate scratch, for nl lights
 __host__ __device__ inline size_t regroup_queue_bytes(int nl) {
