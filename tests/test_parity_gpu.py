@@ -513,3 +513,58 @@ def test_reference_named_host_mirror(rt_ctx, port_oracle):
          "object_id": o["object_id"]}
     st = compare(k, o, normal_fp16=True)
     assert st["color_bad_frac"] <= 1e-3 and st["position_bad"] <= 2, st
+
+
+def _large_scene_with_pathological_objects(size, non_finite=False):
+    """C3 (256 spheres: the large-scene kernels with clusters, light grids and the warp-cooperative scan) with the
+    objects the small edge scenes have, which the conservative tests of those structures must survive: a negative and
+    a zero radius, a sphere around the camera, a huge one far away, a far tiny sphere (the discriminant's worst
+    rounding). non_finite adds NaN / inf centres and radii (their AABBs are what GenerateAABBForObject makes of them):
+    the staging sends such a scene to the literal kernel (a non-finite bound has no place in a box hierarchy)."""
+    from opengl_raytracing_b200 import scene as S
+    w = synthetic.config(3, *size)
+    o = w.objects.copy()
+    sph = [i for i in range(len(o)) if o[i]["type"] == S.SPHERE]
+    o[sph[0]]["radius"] = -abs(float(o[sph[0]]["radius"]))
+    o[sph[1]]["radius"] = 0.0
+    o[sph[2]]["position"] = w.camera.position; o[sph[2]]["radius"] = 2.5        # the camera is inside
+    o[sph[3]]["position"] = (0.0, 0.0, -400.0); o[sph[3]]["radius"] = 150.0
+    o[sph[7]]["position"] = (3.0, 40.0, -300.0); o[sph[7]]["radius"] = 0.05
+    if non_finite:
+        o[sph[4]]["position"] = (np.nan, 0.0, -5.0)
+        o[sph[5]]["radius"] = np.inf
+        o[sph[6]]["position"] = (np.inf, 1.0, -8.0)
+        o[sph[8]]["radius"] = np.nan
+    w.objects = S.generate_aabbs(o)
+    return w
+
+
+def test_large_scene_pathological_objects(rt_ctx, port_oracle):
+    w = _large_scene_with_pathological_objects((256, 144))
+    o = port_oracle.render(w, "port", margins=True)
+    images = {}
+    for kern in (abi.KERNEL_MEGAKERNEL, abi.KERNEL_WAVEFRONT, abi.KERNEL_REGROUP):
+        rt_ctx.set_tuning(kern)
+        try:
+            for flags in (0, abi.FLAG_PARITY_MATH):
+                k = render_workload(rt_ctx, w, flags=flags | abi.FLAG_NORMAL_FP32)
+                assert rt_ctx.get_tuning()["kernel"] == abi.KERNEL_NAMES[kern]
+                st = record(f"large scene with pathological objects, {abi.KERNEL_NAMES[kern]} {'parity-math' if flags else 'fast'} vs port", compare(k, o))
+                assert_parity(st, max_color_frac=2e-3, strict_geom=False)
+                images[(kern, flags)] = k
+        finally:
+            rt_ctx.set_tuning(None)
+    for flags in (0, abi.FLAG_PARITY_MATH):                 # and the three variants agree bit for bit, as everywhere
+        a = images[(abi.KERNEL_MEGAKERNEL, flags)]
+        for kern in (abi.KERNEL_WAVEFRONT, abi.KERNEL_REGROUP):
+            b = images[(kern, flags)]
+            for key in ("color", "position", "normal"):
+                assert np.array_equal(a[key].view(np.uint32), b[key].view(np.uint32)), (kern, flags, key)
+            assert np.array_equal(a["object_id"], b["object_id"]), (kern, flags)
+    # non-finite geometry: the literal kernel takes the scene (and says so), same parity bar
+    w = _large_scene_with_pathological_objects((128, 72), non_finite=True)
+    o = port_oracle.render(w, "port", margins=True)
+    k = render_workload(rt_ctx, w, flags=abi.FLAG_PARITY_MATH | abi.FLAG_NORMAL_FP32)
+    assert rt_ctx.get_tuning()["kernel"] == "literal"
+    st = record("large scene with NaN / inf objects, literal kernel parity-math vs port", compare(k, o))
+    assert_parity(st, max_color_frac=2e-3, strict_geom=False)
