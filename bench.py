@@ -339,8 +339,15 @@ def run_ours(args) -> None:
     stream = torch.cuda.current_stream(dev)
     reducer = None
     if world > 1 and args.shard == "samples" and args.reduce == "peer":
-        reducer = sharding.PeerReducer(ctx, H, W)      # partial frames of every rank mapped into every rank (CUDA IPC)
-        color = reducer.partial                         # (the counter pass; every frame renders into reducer.partial of ITS epoch)
+        try:
+            reducer = sharding.PeerReducer(ctx, H, W)  # partial frames of every rank mapped into every rank (CUDA IPC)
+            color = reducer.partial                     # (the counter pass; every frame renders into reducer.partial of ITS epoch)
+        except sharding.PeerUnavailable as e:           # raised on every rank together: same fallback everywhere
+            if rank == 0:
+                print(f"bench: peer reduce unavailable ({e}); falling back to --reduce nccl", file=sys.stderr)
+            reducer, args.reduce = None, "nccl"
+            args.no_subrecords = True                   # c5_rows maps rank 0's frame the same way
+            par = f"sample ranges x{world} ({ns} spp per rank), partial sums reduced to rank 0 (NCCL reduce; peer mapping unavailable on this box)"
     pipelined = bool(reducer and args.pipeline)
     if pipelined:
         ctx.set_sm_reserve(args.sm_reserve)

@@ -14,6 +14,8 @@ The host logic is backend-agnostic (gloo on CPU in tests/test_sharding.py, nccl 
 """
 from __future__ import annotations
 
+import os
+
 
 def row_range(height: int, rank: int, world: int, align: int = 4) -> tuple:
     """Rows of ``rank``: contiguous, 4-aligned boundaries (the kernel's tile height) so that
@@ -144,6 +146,10 @@ class PeerFrame:
         self.ptr = {}
 
 
+class PeerUnavailable(RuntimeError):
+    """The ranks cannot map each other's memory (no CUDA IPC here); raised on EVERY rank together."""
+
+
 class PeerReducer:
     """The sample-range exchange step without NCCL (one process per GPU): every rank's partial-sum frame, rank 0's
     result frame and a block of flag words per rank are CUDA-IPC mapped into every rank; ``reduce`` enqueues ONE
@@ -175,36 +181,57 @@ class PeerReducer:
         nbytes = height * width * 16
         names = ["partial%d" % i for i in range(self.NBUF)] + ["flags"] + (["result"] if self.rank == 0 else [])
         self.own, handles = {}, torch.zeros(self.NBUF + 2, 64, dtype=torch.uint8)
-        for i, name in enumerate(names):
-            p = C.c_void_p(0)
-            ctx._check(ctx.lib.rt_device_alloc(ctx.handle, C.byref(p), self.FLAG_BYTES if name == "flags" else nbytes))
-            buf = C.create_string_buffer(64)
-            ctx._check(ctx.lib.rt_ipc_export(ctx.handle, p, buf))
-            self.own[name] = p.value
-            handles[i] = torch.tensor(list(buf.raw), dtype=torch.uint8)
+        self.maps, self._opened = [], []
         dev = torch.device("cpu") if dist.get_backend(group) == "gloo" else torch.device("cuda", ctx.device)
-        mine = handles.to(dev)
         torch.cuda.set_device(ctx.device)
-        zero = torch.as_tensor(_DevicePtr(self.own["flags"], (self.FLAG_BYTES // 4,), "<u4"), device=f"cuda:{ctx.device}")
-        zero.view(torch.int32).zero_()
-        torch.cuda.synchronize(ctx.device)
+
+        def agree(ok: bool, what: str, err):
+            """Every rank learns whether EVERY rank got through the step (no rank may wait in a collective for one that
+            raised): all raise PeerUnavailable together, after freeing what they hold."""
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if int(flag.item()) == 0:
+                self.close()
+                raise PeerUnavailable(f"{what} failed on {'this rank: ' + str(err) if err else 'another rank'}")
+
+        err = None
+        try:
+            if os.environ.get("RT_PEER_FORCE_FAIL") == "export":      # dev knob: exercises the fallback of the callers
+                raise RuntimeError("RT_PEER_FORCE_FAIL=export")
+            for i, name in enumerate(names):
+                p = C.c_void_p(0)
+                ctx._check(ctx.lib.rt_device_alloc(ctx.handle, C.byref(p), self.FLAG_BYTES if name == "flags" else nbytes))
+                self.own[name] = p.value
+                buf = C.create_string_buffer(64)
+                ctx._check(ctx.lib.rt_ipc_export(ctx.handle, p, buf))
+                handles[i] = torch.tensor(list(buf.raw), dtype=torch.uint8)
+            zero = torch.as_tensor(_DevicePtr(self.own["flags"], (self.FLAG_BYTES // 4,), "<u4"), device=f"cuda:{ctx.device}")
+            zero.view(torch.int32).zero_()
+            torch.cuda.synchronize(ctx.device)
+        except Exception as e:                                        # noqa: BLE001
+            err = e
+        agree(err is None, "allocating / exporting the peer buffers (CUDA IPC)", err)
+        mine = handles.to(dev)
         everyone = [torch.zeros_like(mine) for _ in range(self.world)]
         dist.all_gather(everyone, mine, group=group)
-        self.maps = []                       # per rank: {name: device address valid in THIS process}
-        self._opened = []
-        for r in range(self.world):
-            if r == self.rank:
-                self.maps.append(dict(self.own))
-                continue
-            hb = everyone[r].cpu().numpy()
-            m = {}
-            for i, name in enumerate(["partial%d" % k for k in range(self.NBUF)] + ["flags"] + (["result"] if r == 0 else [])):
-                p = C.c_void_p(0)
-                ctx._check(ctx.lib.rt_ipc_open(ctx.handle, hb[i].tobytes(), C.byref(p)))
-                m[name] = p.value
-                self._opened.append(p.value)
-            self.maps.append(m)
-        dist.barrier(group=group)            # every flag block is zeroed and mapped before the first epoch
+        try:
+            if os.environ.get("RT_PEER_FORCE_FAIL") == "open" and self.rank == self.world - 1:
+                raise RuntimeError("RT_PEER_FORCE_FAIL=open")
+            for r in range(self.world):
+                if r == self.rank:
+                    self.maps.append(dict(self.own))
+                    continue
+                hb = everyone[r].cpu().numpy()
+                m = {}
+                for i, name in enumerate(["partial%d" % k for k in range(self.NBUF)] + ["flags"] + (["result"] if r == 0 else [])):
+                    p = C.c_void_p(0)
+                    ctx._check(ctx.lib.rt_ipc_open(ctx.handle, hb[i].tobytes(), C.byref(p)))
+                    m[name] = p.value
+                    self._opened.append(p.value)
+                self.maps.append(m)
+        except Exception as e:                                        # noqa: BLE001
+            err = e
+        agree(err is None, "mapping the peers' buffers (CUDA IPC)", err)   # also: every flag block is zeroed and mapped before the first epoch
 
     def _tensor(self, ptr):
         import torch
