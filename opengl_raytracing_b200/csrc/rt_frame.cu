@@ -3,6 +3,7 @@
 // in HBM. Built on the library's own C ABI (rt_render, rt_post_chain, rt_upload_scene): this file
 // adds the image ownership of ForwardShadingPipline::Init (:51-137), the history ping-pong of
 // :141/:236/:249 and the presentation step (default-framebuffer conversion + read-back).
+#include <nvtx3/nvToolsExt.h>
 #include <cuda_runtime.h>
 #include <cstring>
 #include <string>
@@ -103,6 +104,8 @@ rt_status rt_frame_create(rt_context* ctx, int width, int height, rt_frame** out
 void rt_frame_destroy(rt_frame* f) { release(f); }
 
 rt_status rt_frame_render(rt_frame* f, const rt_frame_params* rp, const rt_post_params* pp, void* cuda_stream) {
+  nvtxRangePushA("rt_frame_render");
+  struct Pop { ~Pop() { nvtxRangePop(); } } pop;
   if (!f) return RT_ERR_INVALID_ARG;
   rt_status st = check_params(f, rp, pp, "rt_frame_render");
   if (st != RT_OK) return st;

@@ -6,6 +6,7 @@
 // These are bandwidth-shaped kernels (a few dozen flops per 16-byte texel): one thread per
 // texel (or per short run of texels), 128-bit / 64-bit coalesced accesses along x, read-only
 // data through the non-coherent path so the 9-tap and 3x3 re-reads are served by L1/L2.
+#include <nvtx3/nvToolsExt.h>
 #include <cstdint>
 #include <string>
 #include <cuda_fp16.h>
@@ -696,6 +697,8 @@ rt_status rt_taa_resolve(rt_context* c, const rt_post_params* p, const float* d_
 rt_status rt_post_chain(rt_context* c, const rt_post_params* p, const float* d_color, const void* d_normal,
                         const float* d_history_prev, float* d_history_out, float* d_display, void* cuda_stream) {
   if (!c) return RT_ERR_INVALID_ARG;
+  nvtxRangePushA("rt_post_chain");
+  struct Pop { ~Pop() { nvtxRangePop(); } } pop;
   rt_status st = check_size(c, p, "rt_post_chain");
   if (st != RT_OK) return st;
   if (!d_color || !d_display) return rt::ctx_fail(c, RT_ERR_INVALID_ARG, "rt_post_chain: null image");
