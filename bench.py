@@ -14,9 +14,14 @@ algorithm, counted by the kernel's counter variant (validated against the oracle
 tests/test_parity_gpu.py::test_counters_match_oracle).
 
 N > 1 (torchrun, one rank per GPU): sample-range sharding — every rank renders one
-full frame at its own frameCount, the partial colours are summed on rank 0 with one NCCL
-reduce inside the timed region: per-GPU work is fixed ("weak"). ``--shard rows`` gives the
-strong-scaling row-tile variant (no collective in the data path, tiles gathered to rank 0).
+full frame at its own frameCount, the partial colours are summed into rank 0's frame inside the
+timed region: per-GPU work is fixed ("weak"). The sum is the library's peer pull-reduce kernel
+(rt_peer_reduce over CUDA-IPC mapped partials), pipelined one frame deep: the reduce of frame
+i-1 runs on a second stream, in CTA slots the render grid leaves free (rt_set_sm_reserve),
+inside the timed region of frame i — K timed regions hold K renders and K reduces
+(``--pipeline 0`` / ``--reduce nccl``: the exchange behind the render on one stream).
+``--shard rows`` gives the strong-scaling row-band variant (no collective in the data path:
+every kernel stores straight into rank 0's frame over NVLink).
 """
 from __future__ import annotations
 
