@@ -28,6 +28,7 @@ static int usage() {
                "usage: rt_headless --scene FILE [--size W H] [--frames N] [--depth D] [--samples S] [--flags F]\n"
                "                   [--camera px py pz yaw pitch fov] [--noise FILE W H] [--skybox FILE SIZE CH f16|f32]\n"
                "                   [--device N | --gpus A,B,... [--shard rows|samples]] [--out PREFIX] [--raw] [--post]\n"
+               "                   [--kernel megakernel|wavefront|regroup | --tune]   (one GPU: pin a variant / time them all once)\n"
                "       rt_headless --dump-scene IN.scene OUT.bin\n"
                "       rt_headless --resave IN.scene OUT.scene\n"
                "       rt_headless --resave-v2 IN.scene OUT.scene\n");
@@ -73,7 +74,8 @@ int main(int argc, char** argv) {
   std::string scene, out = "frame", noise_file, sky_file;
   int W = 800, H = 800, frames = 1, depth = 3, samples = 1, device = 0;   // src/global.cpp:4-5: 800 x 800
   int noise_w = 0, noise_h = 0, sky_size = 0, sky_ch = 4;
-  bool sky_f16 = true, raw = false, have_cam = false, post = false;
+  bool sky_f16 = true, raw = false, have_cam = false, post = false, tune = false;
+  int kernel = -1;
   std::vector<int> gpus;
   int sharding = RT_MULTI_ROWS;
   unsigned flags = 0;
@@ -93,6 +95,10 @@ int main(int argc, char** argv) {
     else if (a == "--out") { need(1); out = argv[++i]; }
     else if (a == "--raw") raw = true;
     else if (a == "--post") post = true;
+    else if (a == "--tune") tune = true;
+    else if (a == "--kernel") { need(1); const std::string k = argv[++i];
+      kernel = k == "megakernel" ? RT_KERNEL_MEGAKERNEL : k == "wavefront" ? RT_KERNEL_WAVEFRONT : k == "regroup" ? RT_KERNEL_REGROUP : -2;
+      if (kernel == -2) return usage(); }
     else if (a == "--camera") { need(6); for (int k = 0; k < 6; ++k) cam[k] = (float)std::atof(argv[++i]); have_cam = true; }
     else if (a == "--noise") { need(3); noise_file = argv[++i]; noise_w = std::atoi(argv[++i]); noise_h = std::atoi(argv[++i]); }
     else if (a == "--skybox") { need(4); sky_file = argv[++i]; sky_size = std::atoi(argv[++i]); sky_ch = std::atoi(argv[++i]); sky_f16 = std::string(argv[++i]) == "f16"; }
@@ -123,6 +129,17 @@ int main(int argc, char** argv) {
     pipeline.maxRayDepth = depth;
     pipeline.numSamples = samples;
     pipeline.flags = flags;
+    static const char* const kKernelNames[] = {"megakernel", "wavefront", "literal", "regroup"};
+    if (gpus.empty()) {
+      pipeline.SetAutotune(false);                                // no trial frames inside the loop below
+      if (kernel >= 0) pipeline.PinKernel(kernel);
+      else if (tune) {
+        const rt_tuning t = pipeline.Tune();
+        std::fprintf(stderr, "rt_tune: %s (%d variants:", kKernelNames[t.kernel & 3], t.num_variants);
+        for (int i = 0; i < t.num_variants; ++i) std::fprintf(stderr, " %s %.4f ms", kKernelNames[t.variant_kernel[i] & 3], t.variant_ms[i]);
+        std::fprintf(stderr, ")\n");
+      }
+    }
     const auto t0 = std::chrono::steady_clock::now();
     for (int f = 0; f < frames; ++f) {
       if (post) pipeline.RenderFrame(raw && f == frames - 1);    // the whole iteration: ray tracing + bloom + TAA
@@ -130,9 +147,9 @@ int main(int argc, char** argv) {
     }
     const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     std::printf("{\"scene\": \"%s\", \"objects\": %zu, \"lights\": %zu, \"width\": %d, \"height\": %d, \"frames\": %d, "
-                "\"ms_per_frame_host\": %.4f, \"launches\": %llu}\n",
+                "\"ms_per_frame_host\": %.4f, \"launches\": %llu, \"kernel\": \"%s\"}\n",
                 scene.c_str(), pipeline.ssbo.objects.size(), pipeline.lightSSBO.lights.size(), W, H, frames, ms / frames,
-                (unsigned long long)pipeline.launches());
+                (unsigned long long)pipeline.launches(), gpus.empty() ? kKernelNames[pipeline.LastKernel().kernel & 3] : "per device");
     const size_t px = (size_t)W * H;
     if (post) {                                                  // what the window would show
       if (!WritePPM(out + "_display.ppm", pipeline.displayTex.data(), W, H)) throw std::runtime_error("cannot write " + out + "_display.ppm");

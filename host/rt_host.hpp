@@ -480,6 +480,36 @@ class ForwardShadingPipeline {
     if (taaEnabled) ++frameCount;          // the reference advances frameCount inside the TAA branch (:232-254)
   }
 
+  // Kernel variants (identical images; include/rt_abi.h rt_tune / rt_set_tuning / rt_set_autotune / rt_set_sm_reserve).
+  // No counterpart in the reference (one GLSL program). One GPU only: an rt_multi owns and tunes its contexts itself.
+  rt_tuning Tune() {                       // times every variant on the CURRENT scene and frame shape, keeps the fastest
+    if (multi_) throw std::runtime_error("Tune: one GPU only");
+    if (ssbo.dirty || lightSSBO.dirty) {
+      check(ctx_, rt_upload_scene(ctx_, ssbo.objects.data(), (int)ssbo.objects.size(), lightSSBO.lights.data(),
+                                  (int)lightSSBO.lights.size(), nullptr, 0), "rt_upload_scene");
+      ssbo.dirty = lightSSBO.dirty = false;
+    }
+    SetUniforms();
+    rt_tuning t;
+    check(ctx_, rt_tune(ctx_, &raytracingShader.params, &t), "rt_tune");
+    return t;
+  }
+  void PinKernel(int kernel) {             // RT_KERNEL_MEGAKERNEL / _WAVEFRONT / _REGROUP; -1 removes the pin
+    if (multi_) throw std::runtime_error("PinKernel: one GPU only");
+    if (kernel < 0) { check(ctx_, rt_set_tuning(ctx_, nullptr), "rt_set_tuning"); return; }
+    rt_tuning t;
+    std::memset(&t, 0, sizeof(t));
+    t.kernel = kernel; t.registers = -1; t.phase_level = -1;
+    check(ctx_, rt_set_tuning(ctx_, &t), "rt_set_tuning");
+  }
+  rt_tuning LastKernel() {                 // what the last Render() ran
+    rt_tuning t;
+    check(ctx_, rt_get_tuning(ctx_, nullptr, &t), "rt_get_tuning");
+    return t;
+  }
+  void SetAutotune(bool on) { check(ctx_, rt_set_autotune(ctx_, on ? 1 : 0), "rt_set_autotune"); }
+  void SetSmReserve(int sms) { check(ctx_, rt_set_sm_reserve(ctx_, sms), "rt_set_sm_reserve"); }
+
   // The host's haltonSequence (src/global.cpp), float arithmetic, for the TAA jitter (:242-243).
   static float haltonSequence(int index, int base) {
     float f = 1.0f, r = 0.0f;

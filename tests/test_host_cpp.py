@@ -201,3 +201,26 @@ def test_headless_whole_frames_with_post_chain_match_python_frame(headless, tmp_
     head = b"P6\n%d %d\n255\n" % (W, H)
     assert ppm.startswith(head) and len(ppm) == len(head) + W * H * 3
     assert ppm[len(head):len(head) + 3] == d8[H - 1, 0, :3].tobytes()            # top row first
+
+
+@pytest.mark.gpu
+def test_headless_kernel_pin_and_tune_give_the_same_image(headless, tmp_path):
+    """The C++ host reaches the variant API (rt_set_tuning / rt_tune through ForwardShadingPipeline::PinKernel / Tune):
+    every pinned variant and the tuned choice write the same bytes, and the JSON line names the kernel that ran."""
+    w = synthetic.config(3, 256, 144)
+    p = tmp_path / "c3.scene"
+    p.write_text(S.save_scene(S.Scene(objects=w.objects, lights=w.lights, object_names=[], light_names=[])))
+    images = {}
+    for mode in ("megakernel", "wavefront", "regroup", "tune"):
+        out = str(tmp_path / mode)
+        args = ["--tune"] if mode == "tune" else ["--kernel", mode]
+        r = subprocess.run([headless, "--scene", str(p), "--size", "256", "144", "--frames", "2", "--depth", "4", "--raw", "--out", out] + args,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        info = json.loads(r.stdout.strip().splitlines()[-1])
+        if mode == "tune":
+            assert "rt_tune:" in r.stderr and info["kernel"] in ("megakernel", "wavefront", "regroup")
+        else:
+            assert info["kernel"] == mode
+        images[mode] = open(out + "_color.f32", "rb").read() + open(out + "_position.f32", "rb").read()
+    assert len(set(images.values())) == 1
